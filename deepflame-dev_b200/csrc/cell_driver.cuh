@@ -1,0 +1,137 @@
+// One cell of dfChemistryModel::solveSingle (src/dfChemistryModel/dfChemistryModel.C:738-780)
+// executed by one team: load + normalise Y (setState_TPY, :755), frozen-(T, rho) integration
+// (:757-764), RR_i = (Ynew_i - Yraw_i)/dt*rho_OF and Qdot = -sum hc_i RR_i (:768-772).
+// Shared by the CUDA kernels (kernels.cu) and the host emulation used in tests (tests/emu).
+#pragma once
+#include "integrator.cuh"
+
+namespace dfchem {
+
+struct SolveArgs {
+    int nC;
+    const double* T;
+    const double* p;
+    const double* rho;
+    const double* dt;  // per cell or nullptr
+    double dt_uniform;
+    const double* Y;
+    int ldY;
+    double* RR;
+    int ldRR;
+    double* Qdot;
+    double* cost;  // may be nullptr
+    int* status;   // may be nullptr
+    double rtol, atol;
+    int max_steps;
+};
+
+// set up c (all N species), cs (inert tail), regs.c0/dc; returns rho_ct; ysum via reference
+template <int NP, int NSLOT>
+DFC_HD double load_cell_state(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* regs, int dfc_lane,
+                              const double* Y, int ldY, int cell, double T, double p, double& ysum) {
+    (void)dfc_lane;
+    double* red = sm + m.off_red;
+    double* c = sm + m.off_c;
+    double* cs = sm + m.off_cs;
+    DFC_LANES_BEGIN
+    double s = 0.0;
+    for (int k = tl; k < m.N; k += kTeam) {
+        const double y = Y[(size_t)DFC_LDG(m.perm + k) * ldY + cell];
+        c[k] = y;  // raw mass fraction for now
+        s += y;
+    }
+    red[tl] = s;
+    DFC_LANES_END
+    ysum = team_sum(red);
+    const double rys = 1.0 / ysum;
+    DFC_LANES_BEGIN
+    double s = 0.0;
+    for (int k = tl; k < m.N; k += kTeam) s += c[k] * rys / DFC_LDG(m.W + k);
+    red[tl] = s;
+    DFC_LANES_END
+    const double wbar = 1.0 / team_sum(red);
+    const double rho_ct = p * wbar / (kGasConstant * T);
+    DFC_LANES_BEGIN
+    for (int k = tl; k < m.N; k += kTeam) {
+        const double ck = rho_ct * (c[k] * rys) / DFC_LDG(m.W + k);
+        c[k] = ck;
+        cs[k] = ck;
+    }
+    DFC_LANES_END
+    DFC_LANES_BEGIN
+    DFC_UNROLL
+    for (int s = 0; s < NSLOT; ++s) {
+        const int row = tl + kTeam * s;
+        DFC_LR.c0[s] = row < m.NA ? c[row] : 0.0;
+        DFC_LR.dc[s] = 0.0;
+    }
+    DFC_LANES_END
+    return rho_ct;
+}
+
+template <int NP, int NSLOT>
+DFC_HD void solve_one_cell(const DevMech& m, const SolveArgs& a, double* sm, LaneRegs<NP, NSLOT>* regs,
+                           int dfc_lane, int cell, StepStats& st) {
+    const double T = a.T[cell], p = a.p[cell];
+    const double dt = a.dt ? a.dt[cell] : a.dt_uniform;
+    double ysum;
+    const double rho_ct = load_cell_state<NP, NSLOT>(m, sm, regs, dfc_lane, a.Y, a.ldY, cell, T, p, ysum);
+    setup_rate_constants(m, sm, T, dfc_lane);
+    st = StepStats{0, 0, kCellOk};
+    if (dt > 0.0) st = integrate_cell<NP, NSLOT>(m, sm, regs, dfc_lane, dt, a.rtol, a.atol * rho_ct, a.max_steps);
+    // RR and Qdot
+    const double rho_of = a.rho[cell];
+    const double scale = dt > 0.0 ? rho_of / dt : 0.0;
+    const double rys = 1.0 / ysum;
+    double* red = sm + m.off_red;
+    DFC_LANES_BEGIN
+    double qd = 0.0;
+    DFC_UNROLL
+    for (int s = 0; s < NSLOT; ++s) {
+        const int k = tl + kTeam * s;
+        if (k < m.N) {
+            const int ko = DFC_LDG(m.perm + k);
+            const double yraw = a.Y[(size_t)ko * a.ldY + cell];
+            double dY = yraw * rys - yraw;  // normalisation quirk: RR is taken against the raw Y
+            if (k < m.NA) dY += DFC_LR.dc[s] * DFC_LDG(m.W + k) / rho_ct;
+            const double rr = dY * scale;
+            a.RR[(size_t)ko * a.ldRR + cell] = rr;
+            qd = fma(-DFC_LDG(m.hc + k), rr, qd);
+        }
+    }
+    for (int k = tl + kTeam * NSLOT; k < m.N; k += kTeam) {  // inert tail beyond the row slots
+        const int ko = DFC_LDG(m.perm + k);
+        const double yraw = a.Y[(size_t)ko * a.ldY + cell];
+        const double rr = (yraw * rys - yraw) * scale;
+        a.RR[(size_t)ko * a.ldRR + cell] = rr;
+        qd = fma(-DFC_LDG(m.hc + k), rr, qd);
+    }
+    red[tl] = qd;
+    DFC_LANES_END
+    const double qdot = team_sum(red);
+    DFC_LANES_BEGIN
+    if (tl == 0) {
+        a.Qdot[cell] = qdot;
+        if (a.cost) a.cost[cell] = (double)(st.accepted + st.rejected);
+        if (a.status) a.status[cell] = st.status;
+    }
+    DFC_LANES_END
+}
+
+// calculateW (dfChemistryModel.C:897-923): wrate_i = wdot_i * W_i at (T, p, Y)
+template <int NP, int NSLOT>
+DFC_HD void wdot_one_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* regs, int dfc_lane,
+                          const double* T, const double* p, const double* Y, int ldY, double* wr,
+                          int ldW, int cell) {
+    double ysum;
+    const double Tc = T[cell];
+    load_cell_state<NP, NSLOT>(m, sm, regs, dfc_lane, Y, ldY, cell, Tc, p[cell], ysum);
+    setup_rate_constants(m, sm, Tc, dfc_lane);
+    eval_wdot(m, sm, sm + m.off_c, sm + m.off_vec, dfc_lane, false);
+    DFC_LANES_BEGIN
+    for (int k = tl; k < m.N; k += kTeam)
+        wr[(size_t)DFC_LDG(m.perm + k) * ldW + cell] = k < m.NA ? sm[m.off_vec + k] * DFC_LDG(m.W + k) : 0.0;
+    DFC_LANES_END
+}
+
+}  // namespace dfchem

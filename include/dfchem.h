@@ -1,0 +1,134 @@
+/* dfchem.h -- C ABI of libdfchem_b200.so: B200-native per-cell stiff chemistry integration
+ * and thermo update, the drop-in for the cell-local hot path of DeepFlame's dfChemistryModel.
+ *
+ * Every entry point names the reference interface it replaces (paths relative to the
+ * reference repo show-me-code/deepflame-dev):
+ *
+ *   dfchem_create            Cantera::newSolution(mechanismFile,"") in CanteraMixture
+ *                            src/dfCanteraMixture/CanteraMixture.C:56-68, and the constants the
+ *                            dfChemistryModel ctor caches (species order :234-237, hc_ :335-338,
+ *                            relTol/absTol defaults :57-58).  Flat-ABI precedent:
+ *                            opencc_ode_init(), applications/solvers/dfLowMachFoam/createFields_GPU.H:61
+ *   dfchem_solve[_dev]       dfChemistryModel::solve_CVODE body between getProblems and
+ *                            updateReactionRates, src/dfChemistryModel/dfChemistryModel.C:1010-1083,
+ *                            i.e. solveSingle :738-780 for every cell.  Flat-ABI precedent:
+ *                            opencc_ode_all(), applications/solvers/dfLowMachFoam/YEqn.H:45-74;
+ *                            device-pointer precedent: dfChemistrySolver::Inference,
+ *                            src_gpu/dfChemistrySolver.cu:129-206 (SoA species-major, caller stream)
+ *   dfchem_wdot[_dev]        dfChemistryModel::calculateW, dfChemistryModel.C:897-923
+ *   dfchem_correct_thermo[_dev]  dfChemistryModel::correctThermo cell loop, dfChemistryModel.C:418-543
+ *                            (T from (h,p,Y), psi, rho, cp, hai); device precedent
+ *                            dfThermo::correctThermo, src_gpu/dfThermo.cu:572-671
+ *   dfchem_h_from_T[_dev]    dfChemistryModel::updateEnergy, dfChemistryModel.H:326-352, and the
+ *                            fixesValue(T) patches of correctThermo :572-589; device precedent
+ *                            dfThermo::updateEnergy src_gpu/dfThermo.cu:557-570
+ *   dfchem_balance_plan      LoadBalancer::getOperations (allAverage),
+ *                            src/dfChemistryModel/loadBalancing/LoadBalancer.C:124-180
+ *
+ * Layout: species-major SoA, element (species i, cell c) at  X[i*ld + c]  (the layout of
+ * dfMatrixDataBase::d_y, src_gpu/dfMatrixDataBase.cu:358, and of N separate OpenFOAM fields).
+ * All arithmetic is FP64.  Units are SI-kmol (K, Pa, kg/m3, s, J/kg, kg/m3/s, J/m3/s).
+ * Every function returns 0 on success or a negative DFCHEM_E* code; dfchem_last_error() gives
+ * the message.  There is no CPU fallback: without a usable CUDA device dfchem_create fails.
+ */
+#ifndef DFCHEM_H
+#define DFCHEM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct dfchem_ctx* dfchem_handle;
+
+enum {
+    DFCHEM_OK = 0,
+    DFCHEM_EINVAL = -1,    /* bad argument */
+    DFCHEM_EMECH = -2,     /* mechanism file missing / outside the supported dialect */
+    DFCHEM_ECUDA = -3,     /* CUDA runtime error (no device, launch failure, ...) */
+    DFCHEM_ENOMEM = -4,    /* host or device allocation failed */
+    DFCHEM_EUNSUPPORTED = -5 /* mechanism too large for the compiled kernel set */
+};
+
+/* per-cell status written by dfchem_solve* (ChemistrySolution has no such field; the reference
+ * lets CVODE failures propagate as uncaught exceptions, dfChemistryModel.C:738-780) */
+enum { DFCHEM_CELL_OK = 0, DFCHEM_CELL_MAXSTEPS = 1, DFCHEM_CELL_STEP_UNDERFLOW = 2 };
+
+/* Create a context on CUDA device `device` from a Cantera-YAML mechanism file. */
+int dfchem_create(const char* mech_yaml_path, int device, dfchem_handle* out);
+/* Same, from the flat DFCHEMB1 blob written by the mechanism compiler (dfchem_mechc). */
+int dfchem_create_from_blob(const void* blob, size_t len, int device, dfchem_handle* out);
+void dfchem_destroy(dfchem_handle h);
+const char* dfchem_last_error(dfchem_handle h); /* h may be NULL: error of the failed create */
+
+int dfchem_species_count(dfchem_handle h);
+int dfchem_reaction_count(dfchem_handle h);
+const char* dfchem_species_name(dfchem_handle h, int i); /* Cantera order = YAML phases[0].species */
+int dfchem_species_index(dfchem_handle h, const char* name); /* -1 when absent */
+/* constants (length N, host): which = 0: W [kg/kmol], 1: hc = Hf298SS/W [J/kg] */
+int dfchem_species_constants(dfchem_handle h, int which, double* out);
+
+/* Integrator options; defaults mirror odeCoeffs of CanteraTorchProperties
+ * (relTol 1e-9, absTol 1e-15, dfChemistryModel.C:57-58; ReactorNet max steps 20000). */
+int dfchem_set_tolerances(dfchem_handle h, double rtol, double atol);
+int dfchem_set_max_steps(dfchem_handle h, int max_steps);
+
+/* Chemistry sub-step for nC cells (solveSingle semantics, dfChemistryModel.C:738-780):
+ *   Yn = Y/sum(Y);  rho_ct = p*Wbar/(R*T);  integrate dY/dt = wdot*W/rho_ct at frozen (T, rho_ct)
+ *   over dt;  RR_i = (Ynew_i - Y_i)/dt * rho;  Qdot = -sum_i hc_i*RR_i.
+ * dt: per-cell array (length nC) or NULL to use dt_uniform.  rho is the caller's (OpenFOAM's)
+ * density used only for the RR scaling.  cost (optional, may be NULL) receives the number of
+ * integrator step attempts per cell: it plays the role of ChemistrySolution::cpuTime
+ * (ChemistrySolution.H:44-68) as the load-balancer's input.  status optional (may be NULL).
+ * Host-pointer form: blocking; copies through pinned staging buffers owned by the handle. */
+int dfchem_solve(dfchem_handle h, int nC, const double* T, const double* p, const double* rho,
+                 const double* dt, double dt_uniform, const double* Y, int ldY,
+                 double* RR, int ldRR, double* Qdot, double* cost, int* status);
+/* Device-pointer form: stream-ordered on `stream` (a cudaStream_t passed as void*), no host
+ * synchronisation inside.  All pointers are device pointers on the handle's device. */
+int dfchem_solve_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* rho,
+                     const double* dt, double dt_uniform, const double* Y, int ldY,
+                     double* RR, int ldRR, double* Qdot, double* cost, int* status, void* stream);
+
+/* Instantaneous net production rates wrate_i = wdot_i*W_i [kg/m3/s] at (T, p, Y)
+ * (calculateW, dfChemistryModel.C:897-923). */
+int dfchem_wdot(dfchem_handle h, int nC, const double* T, const double* p, const double* Y,
+                int ldY, double* wrate, int ldW);
+int dfchem_wdot_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* Y,
+                    int ldY, double* wrate, int ldW, void* stream);
+
+/* correctThermo cell loop (dfChemistryModel.C:418-543) without the transport properties:
+ * T: in = initial guess, out = solution of h(T, Y/sum Y) = he (Newton, cp slope, |dT|<=100 K
+ * per iteration, stop |dT| < 1e-9*T);  psi = Wbar/(R T);  rho = p*psi;  cp [J/kg/K] optional;
+ * hai[i*ld + c] = h_i(T)/W_i [J/kg] optional.  n may be cells or boundary faces. */
+int dfchem_correct_thermo(dfchem_handle h, int n, const double* he, const double* p,
+                          const double* Y, int ldY, double* T, double* psi, double* rho,
+                          double* cp, double* hai, int ldH);
+int dfchem_correct_thermo_dev(dfchem_handle h, int n, const double* he, const double* p,
+                              const double* Y, int ldY, double* T, double* psi, double* rho,
+                              double* cp, double* hai, int ldH, void* stream);
+
+/* he = h_mass(T, Y/sum Y) [J/kg]  (updateEnergy, dfChemistryModel.H:326-352). */
+int dfchem_h_from_T(dfchem_handle h, int n, const double* T, const double* Y, int ldY, double* he);
+int dfchem_h_from_T_dev(dfchem_handle h, int n, const double* T, const double* Y, int ldY,
+                        double* he, void* stream);
+
+/* Counters of the last dfchem_solve or dfchem_solve_dev call, summed over its cells (the _dev
+ * form must be synchronised by the caller first): [0] accepted steps, [1] rejected steps,
+ * [2] cells with status != 0, [3] kernel launches issued by the last call. */
+int dfchem_last_counters(dfchem_handle h, unsigned long long out[4]);
+
+/* Load-balancer plan, restating LoadBalancer::getOperations (allAverage rule,
+ * loadBalancing/LoadBalancer.C:124-180) for a cost-weighted all-to-all-v between GPUs:
+ * loads[n_ranks] -> send[from*n_ranks + to] = load units to move (0 on the diagonal);
+ * operations smaller than 1 % of the mean load are dropped as in the reference. */
+int dfchem_balance_plan(const double* loads, int n_ranks, double* send);
+
+const char* dfchem_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DFCHEM_H */

@@ -1,0 +1,121 @@
+// TEST INFRASTRUCTURE: sequential host emulation of the warp-per-cell kernels.
+// Compiles the very same device source (csrc/chem_core.cuh, integrator.cuh, cell_driver.cuh)
+// with a "lane block" = for-loop over the 32 lanes, so the kernel logic and the mechanism
+// tables can be debugged and parity-checked against the oracle on a machine without a GPU.
+// It is never linked into libdfchem_b200.so; only tests/ build and call it.
+#include <cstring>
+#include <stdexcept>
+#include <vector>
+
+#include "../../deepflame-dev_b200/csrc/cell_driver.cuh"
+#include "../../deepflame-dev_b200/csrc/dispatch.hpp"
+
+using namespace dfchem;
+
+namespace {
+struct Emu {
+    HostTables ht;
+    DevMech dm;
+};
+template <int NP, int NSLOT>
+void solve_t(const DevMech& m, const SolveArgs& a, unsigned long long* counters) {
+    std::vector<double> sm(m.cell_doubles, 0.0);
+    std::vector<LaneRegs<NP, NSLOT>> regs(kTeam);
+    for (int cell = 0; cell < a.nC; ++cell) {
+        std::fill(sm.begin(), sm.end(), 0.0);
+        StepStats st;
+        solve_one_cell<NP, NSLOT>(m, a, sm.data(), regs.data(), 0, cell, st);
+        counters[0] += st.accepted;
+        counters[1] += st.rejected;
+        counters[2] += st.status != 0;
+    }
+}
+template <int NP, int NSLOT>
+void wdot_t(const DevMech& m, int nC, const double* T, const double* p, const double* Y, int ldY,
+            double* wr, int ldW) {
+    std::vector<double> sm(m.cell_doubles, 0.0);
+    std::vector<LaneRegs<NP, NSLOT>> regs(kTeam);
+    for (int cell = 0; cell < nC; ++cell)
+        wdot_one_cell<NP, NSLOT>(m, sm.data(), regs.data(), 0, T, p, Y, ldY, wr, ldW, cell);
+}
+// J[i*N + j] = d wdot_i / d c_j (caller species order, inert rows/cols zero) and the inverse check
+template <int NP, int NSLOT>
+void jac_t(const DevMech& m, double T, double p, const double* Y, double inv_hg, double* Jout,
+           double* Ainv_out) {
+    std::vector<double> sm(m.cell_doubles, 0.0);
+    std::vector<LaneRegs<NP, NSLOT>> regs(kTeam);
+    double ysum;
+    load_cell_state<NP, NSLOT>(m, sm.data(), regs.data(), 0, Y, 1, 0, T, p, ysum);
+    setup_rate_constants(m, sm.data(), T, 0);
+    eval_wdot(m, sm.data(), sm.data() + m.off_c, sm.data() + m.off_vec, 0, true);
+    run_gather(m.jac, m.coef, sm.data() + m.off_dq, sm.data() + m.off_J, 0);
+    const double* J = sm.data() + m.off_J;
+    // dense J in caller order incl. the default-efficiency rank-one part and the special columns
+    for (int i = 0; i < m.NA; ++i)
+        for (int j = 0; j < m.N; ++j) {
+            double v = J[m.NA * m.ldj + i];  // gsum: d/dc_j through [M] with default efficiency
+            if (j < m.NA) v += J[j * m.ldj + i];
+            Jout[m.perm[i] * m.N + m.perm[j]] = v;
+        }
+    if (Ainv_out) {
+        gj_invert<NP, NSLOT>(m, sm.data(), regs.data(), 0, inv_hg);
+        for (int i = 0; i < m.NA; ++i)
+            for (int j = 0; j < m.NA; ++j)
+                Ainv_out[i * m.NA + j] = regs[i % kTeam].a[i / kTeam][j] * regs[i % kTeam].invd[i / kTeam];
+    }
+}
+}  // namespace
+
+extern "C" {
+void* emu_create(const void* blob, size_t len) {
+    try {
+        Emu* e = new Emu;
+        Mechanism mech = Mechanism::deserialize(static_cast<const uint8_t*>(blob), len);
+        e->ht = build_tables(mech);
+        e->dm = e->ht.rebase(e->ht.blob.data());
+        return e;
+    } catch (const std::exception&) {
+        return nullptr;
+    }
+}
+void emu_destroy(void* h) { delete static_cast<Emu*>(h); }
+void emu_info(void* h, int* out) {
+    const DevMech& m = static_cast<Emu*>(h)->dm;
+    int v[] = {m.N, m.NA, m.NP, m.R, m.n_msets, m.n_fall, m.n_pow, m.n_dq, m.n_part, m.cell_doubles,
+               m.wdotA.n_iter, m.wdotB.n_iter, m.jac.n_iter, static_cast<Emu*>(h)->ht.jac_entries,
+               static_cast<Emu*>(h)->ht.wdot_entries};
+    std::memcpy(out, v, sizeof(v));
+}
+void emu_perm(void* h, int* out) {
+    const Emu* e = static_cast<Emu*>(h);
+    std::memcpy(out, e->ht.perm.data(), sizeof(int) * e->ht.perm.size());
+}
+int emu_solve(void* h, int nC, const double* T, const double* p, const double* rho, const double* dt,
+              double dt_uniform, const double* Y, int ldY, double* RR, int ldRR, double* Qdot,
+              double* cost, int* status, double rtol, double atol, int max_steps,
+              unsigned long long* counters) {
+    const DevMech& m = static_cast<Emu*>(h)->dm;
+    SolveArgs a{nC, T, p, rho, dt, dt_uniform, Y, ldY, RR, ldRR, Qdot, cost, status, rtol, atol, max_steps};
+    counters[0] = counters[1] = counters[2] = 0;
+#define CALL(NP, NS) solve_t<NP, NS>(m, a, counters)
+    DFC_DISPATCH_NP(m.NP, CALL)
+#undef CALL
+    return 0;
+}
+int emu_wdot(void* h, int nC, const double* T, const double* p, const double* Y, int ldY, double* wr,
+             int ldW) {
+    const DevMech& m = static_cast<Emu*>(h)->dm;
+#define CALL(NP, NS) wdot_t<NP, NS>(m, nC, T, p, Y, ldY, wr, ldW)
+    DFC_DISPATCH_NP(m.NP, CALL)
+#undef CALL
+    return 0;
+}
+int emu_jacobian(void* h, double T, double p, const double* Y, double inv_hg, double* Jout,
+                 double* Ainv_out) {
+    const DevMech& m = static_cast<Emu*>(h)->dm;
+#define CALL(NP, NS) jac_t<NP, NS>(m, T, p, Y, inv_hg, Jout, Ainv_out)
+    DFC_DISPATCH_NP(m.NP, CALL)
+#undef CALL
+    return 0;
+}
+}
