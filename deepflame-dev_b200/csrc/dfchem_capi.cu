@@ -1,0 +1,487 @@
+// C ABI of libdfchem_b200.so (include/dfchem.h).  Host side: mechanism compile -> device tables,
+// launch configuration, chunked H2D/compute/D2H pipeline for the host-pointer entry points.
+// There is deliberately no CPU path here: every entry point runs the sm_100a kernels or fails.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/dfchem.h"
+#include "dispatch.hpp"
+#include "kernels.cuh"
+
+using namespace dfchem;
+
+namespace {
+thread_local std::string g_create_error;
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e == cudaSuccess) cap = bytes;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+constexpr int kSlots = 2;
+}  // namespace
+
+struct dfchem_ctx {
+    int device = 0;
+    Mechanism mech;
+    HostTables ht;
+    void* d_blob = nullptr;
+    DevMech dm{};
+    double rtol = 1e-9, atol = 1e-15;  // dfChemistryModel.C:57-58
+    int max_steps = 20000;             // CVODE default used by ReactorNet
+    int sm_count = 0, solve_blocks_per_sm = 0, wdot_blocks_per_sm = 0;
+    cudaStream_t streams[kSlots] = {nullptr, nullptr};
+    DevBuf slot_in[kSlots], slot_out[kSlots], scratch;
+    unsigned int* d_queue = nullptr;          // kSlots + 1 counters (last: dev API)
+    unsigned long long* d_counters = nullptr; // 3
+    unsigned long long launches = 0;
+    std::string err;
+};
+
+namespace {
+
+int fail(dfchem_ctx* h, int code, const std::string& msg) {
+    if (h) h->err = msg;
+    g_create_error = msg;
+    return code;
+}
+#define CUDA_TRY(h, call)                                                                      \
+    do {                                                                                       \
+        cudaError_t e_ = (call);                                                               \
+        if (e_ != cudaSuccess)                                                                 \
+            return fail(h, DFCHEM_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+template <int NP, int NSLOT>
+cudaError_t configure_t(dfchem_ctx* h) {
+    const size_t smem = (size_t)h->dm.cell_doubles * sizeof(double);
+    cudaError_t e;
+    e = cudaFuncSetAttribute(solve_kernel<NP, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(solve_kernel<NP, NSLOT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(wdot_kernel<NP, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->solve_blocks_per_sm, solve_kernel<NP, NSLOT>, kTeam, smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->wdot_blocks_per_sm, wdot_kernel<NP, NSLOT>, kTeam, smem);
+}
+
+template <int NP, int NSLOT>
+void launch_solve_t(dfchem_ctx* h, const SolveArgs& a, unsigned int* queue, cudaStream_t s) {
+    const size_t smem = (size_t)h->dm.cell_doubles * sizeof(double);
+    const int grid = std::max(1, std::min(h->sm_count * h->solve_blocks_per_sm, a.nC));
+    solve_kernel<NP, NSLOT><<<grid, kTeam, smem, s>>>(h->dm, a, queue, h->d_counters);
+}
+template <int NP, int NSLOT>
+void launch_wdot_t(dfchem_ctx* h, int nC, const double* T, const double* p, const double* Y, int ldY,
+                   double* wr, int ldW, unsigned int* queue, cudaStream_t s) {
+    const size_t smem = (size_t)h->dm.cell_doubles * sizeof(double);
+    const int grid = std::max(1, std::min(h->sm_count * h->wdot_blocks_per_sm, nC));
+    wdot_kernel<NP, NSLOT><<<grid, kTeam, smem, s>>>(h->dm, nC, T, p, Y, ldY, wr, ldW, queue);
+}
+
+int launch_solve(dfchem_ctx* h, const SolveArgs& a, int qslot, cudaStream_t s) {
+    unsigned int* queue = h->d_queue + qslot;
+    CUDA_TRY(h, cudaMemsetAsync(queue, 0, sizeof(unsigned int), s));
+#define CALL(NP, NS) launch_solve_t<NP, NS>(h, a, queue, s)
+    DFC_DISPATCH_NP(h->dm.NP, CALL)
+#undef CALL
+    ++h->launches;
+    CUDA_TRY(h, cudaGetLastError());
+    return DFCHEM_OK;
+}
+
+int finish_create(dfchem_ctx* h, int device, dfchem_handle* out) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        delete h;
+        return fail(nullptr, DFCHEM_ECUDA, "no CUDA device available (libdfchem_b200 has no CPU path)");
+    }
+    if (device < 0 || device >= ndev) {
+        delete h;
+        return fail(nullptr, DFCHEM_EINVAL, "device index out of range");
+    }
+    h->device = device;
+    try {
+        h->ht = build_tables(h->mech);
+    } catch (const std::exception& e) {
+        std::string msg = e.what();
+        delete h;
+        return fail(nullptr, DFCHEM_EUNSUPPORTED, msg);
+    }
+    auto bail = [&](const char* what, cudaError_t e) {
+        std::string msg = std::string(what) + ": " + cudaGetErrorString(e);
+        dfchem_destroy(h);
+        return fail(nullptr, DFCHEM_ECUDA, msg);
+    };
+    cudaError_t e;
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return bail("cudaSetDevice", e);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return bail("cudaGetDeviceProperties", e);
+    h->sm_count = prop.multiProcessorCount;
+    if ((e = cudaMalloc(&h->d_blob, h->ht.blob.size())) != cudaSuccess) return bail("cudaMalloc(tables)", e);
+    if ((e = cudaMemcpy(h->d_blob, h->ht.blob.data(), h->ht.blob.size(), cudaMemcpyHostToDevice)) != cudaSuccess)
+        return bail("cudaMemcpy(tables)", e);
+    h->dm = h->ht.rebase(h->d_blob);
+    if ((e = cudaMalloc(&h->d_queue, (kSlots + 1) * sizeof(unsigned int))) != cudaSuccess) return bail("cudaMalloc", e);
+    if ((e = cudaMalloc(&h->d_counters, 3 * sizeof(unsigned long long))) != cudaSuccess) return bail("cudaMalloc", e);
+    cudaMemset(h->d_counters, 0, 3 * sizeof(unsigned long long));
+    for (int i = 0; i < kSlots; ++i)
+        if ((e = cudaStreamCreateWithFlags(&h->streams[i], cudaStreamNonBlocking)) != cudaSuccess)
+            return bail("cudaStreamCreate", e);
+    e = cudaErrorInvalidValue;
+#define CALL(NP, NS) e = configure_t<NP, NS>(h)
+    DFC_DISPATCH_NP(h->dm.NP, CALL)
+#undef CALL
+    if (e != cudaSuccess) return bail("kernel configuration", e);
+    if (h->solve_blocks_per_sm < 1) return bail("kernel does not fit on an SM", cudaErrorLaunchOutOfResources);
+    *out = h;
+    return DFCHEM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* dfchem_version(void) { return "dfchem-b200 0.1 (sm_100a)"; }
+
+int dfchem_create(const char* mech_yaml_path, int device, dfchem_handle* out) {
+    if (!mech_yaml_path || !out) return fail(nullptr, DFCHEM_EINVAL, "null argument");
+    *out = nullptr;
+    dfchem_ctx* h = new (std::nothrow) dfchem_ctx;
+    if (!h) return fail(nullptr, DFCHEM_ENOMEM, "out of host memory");
+    try {
+        h->mech = compile_mechanism_file(mech_yaml_path);
+    } catch (const std::exception& e) {
+        std::string msg = e.what();
+        delete h;
+        return fail(nullptr, DFCHEM_EMECH, msg);
+    }
+    return finish_create(h, device, out);
+}
+
+int dfchem_create_from_blob(const void* blob, size_t len, int device, dfchem_handle* out) {
+    if (!blob || !out) return fail(nullptr, DFCHEM_EINVAL, "null argument");
+    *out = nullptr;
+    dfchem_ctx* h = new (std::nothrow) dfchem_ctx;
+    if (!h) return fail(nullptr, DFCHEM_ENOMEM, "out of host memory");
+    try {
+        h->mech = Mechanism::deserialize(static_cast<const uint8_t*>(blob), len);
+    } catch (const std::exception& e) {
+        std::string msg = e.what();
+        delete h;
+        return fail(nullptr, DFCHEM_EMECH, msg);
+    }
+    return finish_create(h, device, out);
+}
+
+void dfchem_destroy(dfchem_handle h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    for (int i = 0; i < kSlots; ++i) {
+        if (h->streams[i]) cudaStreamDestroy(h->streams[i]);
+        h->slot_in[i].release();
+        h->slot_out[i].release();
+    }
+    h->scratch.release();
+    if (h->d_blob) cudaFree(h->d_blob);
+    if (h->d_queue) cudaFree(h->d_queue);
+    if (h->d_counters) cudaFree(h->d_counters);
+    delete h;
+}
+
+const char* dfchem_last_error(dfchem_handle h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+int dfchem_species_count(dfchem_handle h) { return h ? h->mech.N : DFCHEM_EINVAL; }
+int dfchem_reaction_count(dfchem_handle h) { return h ? h->mech.R : DFCHEM_EINVAL; }
+const char* dfchem_species_name(dfchem_handle h, int i) {
+    return (h && i >= 0 && i < h->mech.N) ? h->mech.species[i].c_str() : nullptr;
+}
+int dfchem_species_index(dfchem_handle h, const char* name) {
+    if (!h || !name) return -1;
+    for (int i = 0; i < h->mech.N; ++i)
+        if (h->mech.species[i] == name) return i;
+    return -1;
+}
+int dfchem_species_constants(dfchem_handle h, int which, double* out) {
+    if (!h || !out || which < 0 || which > 1) return fail(h, DFCHEM_EINVAL, "bad argument");
+    const std::vector<double>& v = which == 0 ? h->mech.W : h->mech.hc;
+    std::copy(v.begin(), v.end(), out);
+    return DFCHEM_OK;
+}
+int dfchem_set_tolerances(dfchem_handle h, double rtol, double atol) {
+    if (!h || !(rtol > 0) || !(atol >= 0)) return fail(h, DFCHEM_EINVAL, "tolerances must be positive");
+    h->rtol = rtol;
+    h->atol = atol;
+    return DFCHEM_OK;
+}
+int dfchem_set_max_steps(dfchem_handle h, int max_steps) {
+    if (!h || max_steps < 1) return fail(h, DFCHEM_EINVAL, "max_steps must be >= 1");
+    h->max_steps = max_steps;
+    return DFCHEM_OK;
+}
+
+int dfchem_solve_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* rho,
+                     const double* dt, double dt_uniform, const double* Y, int ldY, double* RR,
+                     int ldRR, double* Qdot, double* cost, int* status, void* stream) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC < 0 || (nC > 0 && (!T || !p || !rho || !Y || !RR || !Qdot)) || ldY < nC || ldRR < nC)
+        return fail(h, DFCHEM_EINVAL, "dfchem_solve_dev: bad argument");
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    h->launches = 0;
+    CUDA_TRY(h, cudaMemsetAsync(h->d_counters, 0, 3 * sizeof(unsigned long long), s));
+    ++h->launches;
+    if (nC == 0) return DFCHEM_OK;
+    SolveArgs a{nC, T, p, rho, dt, dt_uniform, Y, ldY, RR, ldRR, Qdot, cost, status, h->rtol, h->atol, h->max_steps};
+    return launch_solve(h, a, kSlots, s);
+}
+
+int dfchem_solve(dfchem_handle h, int nC, const double* T, const double* p, const double* rho,
+                 const double* dt, double dt_uniform, const double* Y, int ldY, double* RR, int ldRR,
+                 double* Qdot, double* cost, int* status) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC < 0 || (nC > 0 && (!T || !p || !rho || !Y || !RR || !Qdot)) || ldY < nC || ldRR < nC)
+        return fail(h, DFCHEM_EINVAL, "dfchem_solve: bad argument");
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    h->launches = 0;
+    CUDA_TRY(h, cudaMemset(h->d_counters, 0, 3 * sizeof(unsigned long long)));
+    const int N = h->mech.N;
+    const int chunk = 1 << 18;
+    // per-slot device staging: in = T,p,rho,dt,Y[N];  out = RR[N],Qdot,cost,status
+    for (int i = 0, c0 = 0; c0 < nC; ++i, c0 += chunk) {
+        const int n = std::min(chunk, nC - c0);
+        const int sl = i % kSlots;
+        cudaStream_t s = h->streams[sl];
+        const size_t ld = (size_t)chunk;
+        CUDA_TRY(h, h->slot_in[sl].ensure((size_t)(N + 4) * ld * sizeof(double)));
+        CUDA_TRY(h, h->slot_out[sl].ensure((size_t)(N + 3) * ld * sizeof(double)));
+        double* din = static_cast<double*>(h->slot_in[sl].p);
+        double* dout = static_cast<double*>(h->slot_out[sl].p);
+        double *dT = din, *dp = din + ld, *drho = din + 2 * ld, *ddt = din + 3 * ld, *dY = din + 4 * ld;
+        double *dRR = dout, *dQ = dout + (size_t)N * ld, *dcost = dQ + ld;
+        int* dstat = reinterpret_cast<int*>(dcost + ld);
+        const size_t nb = (size_t)n * sizeof(double);
+        CUDA_TRY(h, cudaMemcpyAsync(dT, T + c0, nb, cudaMemcpyHostToDevice, s));
+        CUDA_TRY(h, cudaMemcpyAsync(dp, p + c0, nb, cudaMemcpyHostToDevice, s));
+        CUDA_TRY(h, cudaMemcpyAsync(drho, rho + c0, nb, cudaMemcpyHostToDevice, s));
+        if (dt) CUDA_TRY(h, cudaMemcpyAsync(ddt, dt + c0, nb, cudaMemcpyHostToDevice, s));
+        CUDA_TRY(h, cudaMemcpy2DAsync(dY, ld * sizeof(double), Y + c0, (size_t)ldY * sizeof(double), nb, N,
+                                      cudaMemcpyHostToDevice, s));
+        SolveArgs a{n, dT, dp, drho, dt ? ddt : nullptr, dt_uniform, dY, (int)ld, dRR, (int)ld, dQ,
+                    cost ? dcost : nullptr, status ? dstat : nullptr, h->rtol, h->atol, h->max_steps};
+        int rc = launch_solve(h, a, sl, s);
+        if (rc != DFCHEM_OK) return rc;
+        CUDA_TRY(h, cudaMemcpy2DAsync(RR + c0, (size_t)ldRR * sizeof(double), dRR, ld * sizeof(double), nb, N,
+                                      cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(h, cudaMemcpyAsync(Qdot + c0, dQ, nb, cudaMemcpyDeviceToHost, s));
+        if (cost) CUDA_TRY(h, cudaMemcpyAsync(cost + c0, dcost, nb, cudaMemcpyDeviceToHost, s));
+        if (status) CUDA_TRY(h, cudaMemcpyAsync(status + c0, dstat, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s));
+    }
+    for (int sl = 0; sl < kSlots; ++sl) CUDA_TRY(h, cudaStreamSynchronize(h->streams[sl]));
+    return DFCHEM_OK;
+}
+
+int dfchem_last_counters(dfchem_handle h, unsigned long long out[4]) {
+    if (!h || !out) return DFCHEM_EINVAL;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    CUDA_TRY(h, cudaMemcpy(out, h->d_counters, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    out[3] = h->launches;
+    return DFCHEM_OK;
+}
+
+int dfchem_wdot_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* Y, int ldY,
+                    double* wrate, int ldW, void* stream) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC < 0 || (nC > 0 && (!T || !p || !Y || !wrate)) || ldY < nC || ldW < nC)
+        return fail(h, DFCHEM_EINVAL, "dfchem_wdot_dev: bad argument");
+    if (nC == 0) return DFCHEM_OK;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    unsigned int* queue = h->d_queue + kSlots;
+    CUDA_TRY(h, cudaMemsetAsync(queue, 0, sizeof(unsigned int), s));
+#define CALL(NP, NS) launch_wdot_t<NP, NS>(h, nC, T, p, Y, ldY, wrate, ldW, queue, s)
+    DFC_DISPATCH_NP(h->dm.NP, CALL)
+#undef CALL
+    CUDA_TRY(h, cudaGetLastError());
+    return DFCHEM_OK;
+}
+
+int dfchem_wdot(dfchem_handle h, int nC, const double* T, const double* p, const double* Y, int ldY,
+                double* wrate, int ldW) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC < 0 || (nC > 0 && (!T || !p || !Y || !wrate)) || ldY < nC || ldW < nC)
+        return fail(h, DFCHEM_EINVAL, "dfchem_wdot: bad argument");
+    if (nC == 0) return DFCHEM_OK;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    const int N = h->mech.N;
+    const size_t ld = (size_t)nC, nb = ld * sizeof(double);
+    CUDA_TRY(h, h->scratch.ensure((2 * (size_t)N + 2) * nb));
+    double* d = static_cast<double*>(h->scratch.p);
+    double *dT = d, *dp = d + ld, *dY = d + 2 * ld, *dW = dY + (size_t)N * ld;
+    cudaStream_t s = h->streams[0];
+    CUDA_TRY(h, cudaMemcpyAsync(dT, T, nb, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(h, cudaMemcpyAsync(dp, p, nb, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(h, cudaMemcpy2DAsync(dY, nb, Y, (size_t)ldY * sizeof(double), nb, N, cudaMemcpyHostToDevice, s));
+    int rc = dfchem_wdot_dev(h, nC, dT, dp, dY, nC, dW, nC, s);
+    if (rc != DFCHEM_OK) return rc;
+    CUDA_TRY(h, cudaMemcpy2DAsync(wrate, (size_t)ldW * sizeof(double), dW, nb, nb, N, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(h, cudaStreamSynchronize(s));
+    return DFCHEM_OK;
+}
+
+int dfchem_correct_thermo_dev(dfchem_handle h, int n, const double* he, const double* p, const double* Y,
+                              int ldY, double* T, double* psi, double* rho, double* cp, double* hai,
+                              int ldH, void* stream) {
+    if (!h) return DFCHEM_EINVAL;
+    if (n < 0 || (n > 0 && (!he || !p || !Y || !T || !psi || !rho)) || ldY < n || (hai && ldH < n))
+        return fail(h, DFCHEM_EINVAL, "dfchem_correct_thermo_dev: bad argument");
+    if (n == 0) return DFCHEM_OK;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int grid = (n + 255) / 256, N = h->mech.N;
+    if (N <= 8) thermo_kernel<8><<<grid, 256, 0, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
+    else if (N <= 16) thermo_kernel<16><<<grid, 256, 0, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
+    else if (N <= 24) thermo_kernel<24><<<grid, 256, 0, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
+    else if (N <= 40) thermo_kernel<40><<<grid, 256, 0, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
+    else if (N <= 64) thermo_kernel<64><<<grid, 256, 0, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
+    else return fail(h, DFCHEM_EUNSUPPORTED, "thermo kernel supports at most 64 species");
+    CUDA_TRY(h, cudaGetLastError());
+    return DFCHEM_OK;
+}
+
+int dfchem_correct_thermo(dfchem_handle h, int n, const double* he, const double* p, const double* Y,
+                          int ldY, double* T, double* psi, double* rho, double* cp, double* hai, int ldH) {
+    if (!h) return DFCHEM_EINVAL;
+    if (n < 0 || (n > 0 && (!he || !p || !Y || !T || !psi || !rho)) || ldY < n || (hai && ldH < n))
+        return fail(h, DFCHEM_EINVAL, "dfchem_correct_thermo: bad argument");
+    if (n == 0) return DFCHEM_OK;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    const int N = h->mech.N;
+    const size_t ld = (size_t)n, nb = ld * sizeof(double);
+    CUDA_TRY(h, h->scratch.ensure((2 * (size_t)N + 6) * nb));
+    double* d = static_cast<double*>(h->scratch.p);
+    double *dhe = d, *dp = d + ld, *dT = d + 2 * ld, *dpsi = d + 3 * ld, *drho = d + 4 * ld, *dcp = d + 5 * ld;
+    double *dY = d + 6 * ld, *dH = dY + (size_t)N * ld;
+    cudaStream_t s = h->streams[0];
+    CUDA_TRY(h, cudaMemcpyAsync(dhe, he, nb, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(h, cudaMemcpyAsync(dp, p, nb, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(h, cudaMemcpyAsync(dT, T, nb, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(h, cudaMemcpy2DAsync(dY, nb, Y, (size_t)ldY * sizeof(double), nb, N, cudaMemcpyHostToDevice, s));
+    int rc = dfchem_correct_thermo_dev(h, n, dhe, dp, dY, n, dT, dpsi, drho, cp ? dcp : nullptr,
+                                       hai ? dH : nullptr, n, s);
+    if (rc != DFCHEM_OK) return rc;
+    CUDA_TRY(h, cudaMemcpyAsync(T, dT, nb, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(h, cudaMemcpyAsync(psi, dpsi, nb, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(h, cudaMemcpyAsync(rho, drho, nb, cudaMemcpyDeviceToHost, s));
+    if (cp) CUDA_TRY(h, cudaMemcpyAsync(cp, dcp, nb, cudaMemcpyDeviceToHost, s));
+    if (hai)
+        CUDA_TRY(h, cudaMemcpy2DAsync(hai, (size_t)ldH * sizeof(double), dH, nb, nb, N, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(h, cudaStreamSynchronize(s));
+    return DFCHEM_OK;
+}
+
+int dfchem_h_from_T_dev(dfchem_handle h, int n, const double* T, const double* Y, int ldY, double* he,
+                        void* stream) {
+    if (!h) return DFCHEM_EINVAL;
+    if (n < 0 || (n > 0 && (!T || !Y || !he)) || ldY < n) return fail(h, DFCHEM_EINVAL, "dfchem_h_from_T_dev: bad argument");
+    if (n == 0) return DFCHEM_OK;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    enthalpy_kernel<<<(n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(h->dm, n, T, Y, ldY, he);
+    CUDA_TRY(h, cudaGetLastError());
+    return DFCHEM_OK;
+}
+
+int dfchem_h_from_T(dfchem_handle h, int n, const double* T, const double* Y, int ldY, double* he) {
+    if (!h) return DFCHEM_EINVAL;
+    if (n < 0 || (n > 0 && (!T || !Y || !he)) || ldY < n) return fail(h, DFCHEM_EINVAL, "dfchem_h_from_T: bad argument");
+    if (n == 0) return DFCHEM_OK;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    const int N = h->mech.N;
+    const size_t ld = (size_t)n, nb = ld * sizeof(double);
+    CUDA_TRY(h, h->scratch.ensure(((size_t)N + 2) * nb));
+    double* d = static_cast<double*>(h->scratch.p);
+    cudaStream_t s = h->streams[0];
+    CUDA_TRY(h, cudaMemcpyAsync(d, T, nb, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(h, cudaMemcpy2DAsync(d + 2 * ld, nb, Y, (size_t)ldY * sizeof(double), nb, N, cudaMemcpyHostToDevice, s));
+    int rc = dfchem_h_from_T_dev(h, n, d, d + 2 * ld, n, d + ld, s);
+    if (rc != DFCHEM_OK) return rc;
+    CUDA_TRY(h, cudaMemcpyAsync(he, d + ld, nb, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(h, cudaStreamSynchronize(s));
+    return DFCHEM_OK;
+}
+
+int dfchem_bench_fp64_peak(int device, double* tflops) {
+    if (!tflops) return DFCHEM_EINVAL;
+    if (cudaSetDevice(device) != cudaSuccess) return DFCHEM_ECUDA;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return DFCHEM_ECUDA;
+    double* d = nullptr;
+    if (cudaMalloc(&d, sizeof(double)) != cudaSuccess) return DFCHEM_ECUDA;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int grid = prop.multiProcessorCount * 8, iters = 20000;
+    double best = 0.0;
+    for (int rep = 0; rep < 5; ++rep) {
+        cudaEventRecord(e0);
+        fp64_peak_kernel<<<grid, 256>>>(d, iters, 1.0 + rep);
+        cudaEventRecord(e1);
+        if (cudaEventSynchronize(e1) != cudaSuccess) break;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double flops = 2.0 * 16.0 * (double)iters * 256.0 * grid;
+        if (rep > 0 && ms > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    *tflops = best;
+    return cudaGetLastError() == cudaSuccess && best > 0 ? DFCHEM_OK : DFCHEM_ECUDA;
+}
+
+// allAverage rule of LoadBalancer::getOperations (loadBalancing/LoadBalancer.C:124-180): sort
+// ranks by load, repeatedly pair the heaviest sender with the lightest receiver and move
+// min(sender - mean, mean - receiver); drop operations below 1 % of the mean.
+int dfchem_balance_plan(const double* loads, int n, double* send) {
+    if (!loads || !send || n < 1) return DFCHEM_EINVAL;
+    std::fill(send, send + (size_t)n * n, 0.0);
+    double mean = 0.0;
+    for (int i = 0; i < n; ++i) mean += loads[i];
+    mean /= n;
+    std::vector<int> order(n);
+    for (int i = 0; i < n; ++i) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return loads[a] < loads[b]; });
+    std::vector<double> v(n);
+    for (int i = 0; i < n; ++i) v[i] = loads[order[i]];
+    int lo = 0, hi = n - 1;  // lightest receiver, heaviest sender
+    while (lo < hi) {
+        const double give = v[hi] - mean, take = mean - v[lo];
+        if (!(give > 0.0) || !(take > 0.0)) break;
+        const double x = std::min(give, take);
+        if (x > 0.01 * mean) send[(size_t)order[hi] * n + order[lo]] += x;
+        v[hi] -= x;
+        v[lo] += x;
+        if (v[hi] - mean <= 1e-12 * mean) --hi;
+        if (mean - v[lo] <= 1e-12 * mean) ++lo;
+    }
+    return DFCHEM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,161 @@
+// sm_100a kernels of libdfchem_b200: warp-per-cell integrator with a dynamic work queue, the
+// instantaneous-rate kernel, and the thread-per-cell thermo kernels.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "cell_driver.cuh"
+
+namespace dfchem {
+
+// counters[0] accepted steps, [1] rejected steps, [2] failed cells
+template <int NP, int NSLOT>
+__global__ void __launch_bounds__(kTeam)
+solve_kernel(const DevMech m, const SolveArgs a, unsigned int* queue, unsigned long long* counters) {
+    extern __shared__ double2 dfc_smem[];
+    double* sm = reinterpret_cast<double*>(dfc_smem);
+    const int lane = threadIdx.x;
+    LaneRegs<NP, NSLOT> regs;
+    // Jacobian entries that no reaction touches stay zero for the whole launch
+    for (int i = lane; i < (m.NA + 1) * m.ldj; i += kTeam) sm[m.off_J + i] = 0.0;
+    __syncwarp();
+    unsigned long long acc = 0, rej = 0, bad = 0;
+    while (true) {
+        // per-warp dynamic work queue: stiff cells keep their warp, the others move on
+        int cell = 0;
+        if (lane == 0) cell = (int)atomicAdd(queue, 1u);
+        cell = __shfl_sync(0xffffffffu, cell, 0);
+        if (cell >= a.nC) break;
+        StepStats st;
+        solve_one_cell<NP, NSLOT>(m, a, sm, &regs, lane, cell, st);
+        acc += st.accepted;
+        rej += st.rejected;
+        bad += st.status != kCellOk;
+    }
+    if (lane == 0) {
+        atomicAdd(counters + 0, acc);
+        atomicAdd(counters + 1, rej);
+        atomicAdd(counters + 2, bad);
+    }
+}
+
+template <int NP, int NSLOT>
+__global__ void __launch_bounds__(kTeam)
+wdot_kernel(const DevMech m, int nC, const double* T, const double* p, const double* Y, int ldY,
+            double* wr, int ldW, unsigned int* queue) {
+    extern __shared__ double2 dfc_smem[];
+    double* sm = reinterpret_cast<double*>(dfc_smem);
+    const int lane = threadIdx.x;
+    LaneRegs<NP, NSLOT> regs;
+    while (true) {
+        int cell = 0;
+        if (lane == 0) cell = (int)atomicAdd(queue, 1u);
+        cell = __shfl_sync(0xffffffffu, cell, 0);
+        if (cell >= nC) break;
+        wdot_one_cell<NP, NSLOT>(m, sm, &regs, lane, T, p, Y, ldY, wr, ldW, cell);
+    }
+}
+
+// ---- thermo: thread per cell, species-major loads are coalesced across the warp ---------------
+// correctThermo cell body (dfChemistryModel.C:494-511) without transport: normalise Y, Newton on
+// T with cp as slope (setState_HP; same iteration as src_gpu/dfThermo.cu:296-320 with Cantera's
+// 100 K step limit), psi = Wbar/(R T), rho = p psi, optional cp and hai_i = h_i/W_i.
+template <int NMAX>
+__global__ void __launch_bounds__(256)
+thermo_kernel(const DevMech m, int n, const double* __restrict__ he, const double* __restrict__ p,
+              const double* __restrict__ Y, int ldY, double* __restrict__ T, double* __restrict__ psi,
+              double* __restrict__ rho, double* __restrict__ cp_out, double* __restrict__ hai, int ldH) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n) return;
+    // y[k] = Y_k / (sum Y * W_k) * R   (mass fraction over molar mass, times R), internal order
+    double y[NMAX];
+    double ysum = 0.0;
+#pragma unroll
+    for (int k = 0; k < NMAX; ++k) {
+        y[k] = 0.0;
+        if (k < m.N) {
+            y[k] = Y[(size_t)__ldg(m.perm + k) * ldY + c];
+            ysum += y[k];
+        }
+    }
+    const double rys = 1.0 / ysum;
+    double rw = 0.0;
+#pragma unroll
+    for (int k = 0; k < NMAX; ++k)
+        if (k < m.N) {
+            y[k] = y[k] * rys / __ldg(m.W + k);
+            rw += y[k];
+        }
+    const double htarget = he[c];
+    double Tc = T[c];
+    double cp = 0.0;
+    for (int it = 0; it < 60; ++it) {
+        double h = 0.0;
+        cp = 0.0;
+#pragma unroll
+        for (int k = 0; k < NMAX; ++k)
+            if (k < m.N) {
+                const double* a = nasa_sel(m, k, Tc);
+                h = fma(y[k], nasa_h_RT(a, Tc), h);
+                cp = fma(y[k], nasa_cp_R(a, Tc), cp);
+            }
+        h *= kGasConstant * Tc;
+        cp *= kGasConstant;
+        double dT = (h - htarget) / cp;
+        dT = fmax(-100.0, fmin(100.0, dT));
+        Tc -= dT;
+        if (fabs(dT) < 1e-10 * Tc) break;
+    }
+    T[c] = Tc;
+    const double ps = 1.0 / (rw * kGasConstant * Tc);  // Wbar/(R T)
+    psi[c] = ps;
+    rho[c] = p[c] * ps;
+    if (cp_out) {
+        cp = 0.0;
+#pragma unroll
+        for (int k = 0; k < NMAX; ++k)
+            if (k < m.N) cp = fma(y[k], nasa_cp_R(nasa_sel(m, k, Tc), Tc), cp);
+        cp_out[c] = cp * kGasConstant;
+    }
+    if (hai) {
+        const double RT = kGasConstant * Tc;
+#pragma unroll
+        for (int k = 0; k < NMAX; ++k)
+            if (k < m.N)
+                hai[(size_t)__ldg(m.perm + k) * ldH + c] = nasa_h_RT(nasa_sel(m, k, Tc), Tc) * RT / __ldg(m.W + k);
+    }
+}
+
+// FP64 roofline denominator: 16 independent DFMA chains per thread (MEASURED_PEAKS.json has no
+// FP64 entry).  2 flops per DFMA.
+__global__ void __launch_bounds__(256) fp64_peak_kernel(double* out, int iters, double seed) {
+    double a[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) a[i] = seed + i + threadIdx.x * 1e-3;
+    const double b = 1.0000001, c = 1e-9;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) a[i] = fma(a[i], b, c);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s += a[i];
+    if (s == 12345.678) out[0] = s;  // never true; keeps the chains alive
+}
+
+// updateEnergy (dfChemistryModel.H:326-352): he = h_mass(T, Y/sum Y)
+__global__ void __launch_bounds__(256)
+enthalpy_kernel(const DevMech m, int n, const double* __restrict__ T, const double* __restrict__ Y,
+                int ldY, double* __restrict__ he) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n) return;
+    const double Tc = T[c];
+    double ysum = 0.0, h = 0.0;
+    for (int k = 0; k < m.N; ++k) {
+        const double y = Y[(size_t)__ldg(m.perm + k) * ldY + c];
+        ysum += y;
+        h = fma(y / __ldg(m.W + k), nasa_h_RT(nasa_sel(m, k, Tc), Tc), h);
+    }
+    he[c] = h * kGasConstant * Tc / ysum;
+}
+
+}  // namespace dfchem

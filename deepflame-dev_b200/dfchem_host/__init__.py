@@ -1,0 +1,180 @@
+"""Host-side mirror of the reference's chemistry interface, bound to libdfchem_b200.so via ctypes.
+
+`DfChemistryModel` keeps the OpenFOAM-facing surface of the reference class
+`Foam::dfChemistryModel<ThermoType>` (src/dfChemistryModel/dfChemistryModel.H:281-354) for the
+hot path: `solve(deltaT)`, `RR(i)`, `Qdot()`, `correctThermo()`, `updateEnergy()`,
+`calculateW()`/`wrate(i)`, `species()`, `Y()`.  Fields are plain NumPy arrays in the
+reference's layout (one contiguous array per species = species-major SoA).  All arithmetic runs
+in the CUDA library; there is no NumPy/CPU fallback: if the library or a GPU is missing the
+constructor raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_double, c_int, c_size_t, c_ulonglong, c_void_p
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libdfchem_b200.so")
+GREAT = 1.0e15  # OpenFOAM's `great` (double precision), returned by updateReactionRates (.C:871,894)
+
+_dp = POINTER(c_double)
+_ip = POINTER(c_int)
+
+# every symbol include/dfchem.h declares: (restype, argtypes)
+SIGNATURES = {
+    "dfchem_create": (c_int, [c_char_p, c_int, POINTER(c_void_p)]),
+    "dfchem_create_from_blob": (c_int, [c_void_p, c_size_t, c_int, POINTER(c_void_p)]),
+    "dfchem_destroy": (None, [c_void_p]),
+    "dfchem_last_error": (c_char_p, [c_void_p]),
+    "dfchem_species_count": (c_int, [c_void_p]),
+    "dfchem_reaction_count": (c_int, [c_void_p]),
+    "dfchem_species_name": (c_char_p, [c_void_p, c_int]),
+    "dfchem_species_index": (c_int, [c_void_p, c_char_p]),
+    "dfchem_species_constants": (c_int, [c_void_p, c_int, _dp]),
+    "dfchem_set_tolerances": (c_int, [c_void_p, c_double, c_double]),
+    "dfchem_set_max_steps": (c_int, [c_void_p, c_int]),
+    "dfchem_solve": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_double, c_void_p,
+                             c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    "dfchem_solve_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_double, c_void_p,
+                                 c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "dfchem_wdot": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int]),
+    "dfchem_wdot_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]),
+    "dfchem_correct_thermo": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                                      c_void_p, c_void_p, c_void_p, c_int]),
+    "dfchem_correct_thermo_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                                          c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "dfchem_h_from_T": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
+    "dfchem_h_from_T_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "dfchem_last_counters": (c_int, [c_void_p, POINTER(c_ulonglong)]),
+    "dfchem_balance_plan": (c_int, [_dp, c_int, _dp]),
+    "dfchem_bench_fp64_peak": (c_int, [c_int, _dp]),
+    "dfchem_version": (c_char_p, []),
+}
+
+_lib = None
+
+
+def load_library(path: str = LIB_PATH):
+    """dlopen libdfchem_b200.so and type every export.  Raises if the library is missing."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(path):
+            raise RuntimeError(f"{path} not found: build it with `python __graft_entry__.py` "
+                               "(there is no CPU fallback)")
+        lib = ctypes.CDLL(path)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+class DfchemError(RuntimeError):
+    pass
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return c_void_p(a)
+    return c_void_p(a.ctypes.data)
+
+
+class Handle:
+    """Thin RAII wrapper over dfchem_handle."""
+
+    def __init__(self, mechanism: str | bytes, device: int = 0):
+        self.lib = load_library()
+        h = c_void_p()
+        if isinstance(mechanism, (bytes, bytearray)):
+            buf = ctypes.create_string_buffer(bytes(mechanism), len(mechanism))
+            rc = self.lib.dfchem_create_from_blob(ctypes.cast(buf, c_void_p), len(mechanism), device, ctypes.byref(h))
+        else:
+            rc = self.lib.dfchem_create(os.fsencode(mechanism), device, ctypes.byref(h))
+        if rc != 0:
+            raise DfchemError(f"dfchem_create failed ({rc}): {self.lib.dfchem_last_error(None).decode()}")
+        self.h = h
+        self.N = self.lib.dfchem_species_count(h)
+        self.R = self.lib.dfchem_reaction_count(h)
+        self.species = [self.lib.dfchem_species_name(h, i).decode() for i in range(self.N)]
+        self.W = np.zeros(self.N)
+        self.hc = np.zeros(self.N)
+        self.check(self.lib.dfchem_species_constants(h, 0, self.W.ctypes.data_as(_dp)))
+        self.check(self.lib.dfchem_species_constants(h, 1, self.hc.ctypes.data_as(_dp)))
+
+    def check(self, rc):
+        if rc != 0:
+            raise DfchemError(f"dfchem error {rc}: {self.lib.dfchem_last_error(self.h).decode()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.dfchem_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_tolerances(self, rtol, atol):
+        self.check(self.lib.dfchem_set_tolerances(self.h, rtol, atol))
+
+    def counters(self):
+        out = (c_ulonglong * 4)()
+        self.check(self.lib.dfchem_last_counters(self.h, out))
+        return dict(accepted=out[0], rejected=out[1], failed=out[2], launches=out[3])
+
+    # ---- host-pointer entry points (NumPy arrays; Y, RR are [N, ld] C-contiguous) --------
+    def solve(self, T, p, rho, dt, Y, RR=None, Qdot=None, cost=None, status=None):
+        nC = T.shape[0]
+        assert Y.shape[0] == self.N and Y.flags.c_contiguous and Y.dtype == np.float64
+        RR = np.empty((self.N, nC)) if RR is None else RR
+        Qdot = np.empty(nC) if Qdot is None else Qdot
+        dt_arr = None if np.isscalar(dt) else np.ascontiguousarray(dt, dtype=np.float64)
+        self.check(self.lib.dfchem_solve(self.h, nC, _ptr(T), _ptr(p), _ptr(rho), _ptr(dt_arr),
+                                         float(dt) if dt_arr is None else 0.0, _ptr(Y), Y.shape[1],
+                                         _ptr(RR), RR.shape[1], _ptr(Qdot), _ptr(cost), _ptr(status)))
+        return RR, Qdot
+
+    def wdot(self, T, p, Y):
+        nC = T.shape[0]
+        out = np.empty((self.N, nC))
+        self.check(self.lib.dfchem_wdot(self.h, nC, _ptr(T), _ptr(p), _ptr(Y), Y.shape[1], _ptr(out), nC))
+        return out
+
+    def correct_thermo(self, he, p, Y, T, want_cp=False, want_hai=False):
+        n = he.shape[0]
+        T = np.array(T, dtype=np.float64, copy=True)
+        psi = np.empty(n)
+        rho = np.empty(n)
+        cp = np.empty(n) if want_cp else None
+        hai = np.empty((self.N, n)) if want_hai else None
+        self.check(self.lib.dfchem_correct_thermo(self.h, n, _ptr(he), _ptr(p), _ptr(Y), Y.shape[1], _ptr(T),
+                                                  _ptr(psi), _ptr(rho), _ptr(cp), _ptr(hai), n))
+        return T, psi, rho, cp, hai
+
+    def h_from_T(self, T, Y):
+        n = T.shape[0]
+        he = np.empty(n)
+        self.check(self.lib.dfchem_h_from_T(self.h, n, _ptr(T), _ptr(Y), Y.shape[1], _ptr(he)))
+        return he
+
+
+def balance_plan(loads):
+    lib = load_library()
+    loads = np.ascontiguousarray(loads, dtype=np.float64)
+    n = loads.shape[0]
+    send = np.zeros((n, n))
+    rc = lib.dfchem_balance_plan(loads.ctypes.data_as(_dp), n, send.ctypes.data_as(_dp))
+    if rc != 0:
+        raise DfchemError(f"dfchem_balance_plan failed ({rc})")
+    return send
+
+
+from .model import DfChemistryModel  # noqa: E402,F401

@@ -1,0 +1,100 @@
+"""`DfChemistryModel`: the reference's `dfChemistryModel<ThermoType>` surface on NumPy fields.
+
+Reference (read-only): src/dfChemistryModel/dfChemistryModel.{H,C}
+  ctor             .C:34-339   reads CanteraTorchProperties: chemistry, CanteraMechanismFile,
+                               odeCoeffs{relTol,absTol} (defaults 1e-9 / 1e-15, :57-58)
+  solve(scalar)    .C:386-399  returns min(solve<>(UniformField(deltaT)), 2*deltaT)
+  solve(field)     .C:401-408  returns solve<>(deltaT)           (= great, see below)
+  solve_CVODE      .C:1010-1083 `if(!chemistry_) return great`; RR_, Qdot_, cpuTimes_ are filled
+  updateReactionRates .C:863-895 returns deltaTMin = great unconditionally
+  correctThermo    .C:418-543  T from (ha, p, Y); psi = W/(R T); rho = p psi
+  updateEnergy     .H:326-352  he = h_mass(T, p, Y)
+  calculateW       .C:897-923  wrate_i = wdot_i W_i
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import GREAT, Handle
+
+
+class DfChemistryModel:
+    """Fields (all float64 NumPy arrays of length nCells; `Y`, `RR` are [nSpecies, nCells]):
+    T, p, rho, he (absolute enthalpy `ha`), psi, Y.  They play the role of the volScalarFields
+    the reference class holds references to (dfChemistryModel.H:100-131)."""
+
+    def __init__(self, mechanism_file, n_cells, *, chemistry=True, rel_tol=1e-9, abs_tol=1e-15, device=0):
+        self._h = Handle(mechanism_file, device)
+        self.chemistry_ = bool(chemistry)
+        self.relTol_, self.absTol_ = float(rel_tol), float(abs_tol)
+        self._h.set_tolerances(self.relTol_, self.absTol_)
+        n, N = int(n_cells), self._h.N
+        self.T = np.full(n, 300.0)
+        self.p = np.full(n, 101325.0)
+        self.rho = np.ones(n)
+        self.he = np.zeros(n)
+        self.psi = np.zeros(n)
+        self._Y = np.zeros((N, n))
+        self._RR = np.zeros((N, n))
+        self._wrate = np.zeros((N, n))
+        self._Qdot = np.zeros(n)
+        self.cpuTimes_ = np.zeros(n)       # per-cell cost (step attempts); ChemistrySolution::cpuTime analogue
+        self.cellStatus_ = np.zeros(n, dtype=np.int32)
+        self.hc_ = self._h.hc.copy()       # Hf298SS/W  (.C:335-338)
+
+    # ---- accessors (dfChemistryModel.H:281-324) ------------------------------------------
+    def species(self):
+        return list(self._h.species)
+
+    def nSpecies(self):
+        return self._h.N
+
+    def nReactions(self):
+        return self._h.R
+
+    def Y(self):
+        return self._Y
+
+    def RR(self, i):
+        return self._RR[i]
+
+    def wrate(self, i):
+        return self._wrate[i]
+
+    def Qdot(self):
+        return self._Qdot
+
+    def W(self):
+        return self._h.W
+
+    # ---- hot path ------------------------------------------------------------------------
+    def solve(self, deltaT):
+        """Chemistry sub-step.  scalar deltaT -> min(great, 2*deltaT); field deltaT -> great."""
+        scalar = np.isscalar(deltaT)
+        if not self.chemistry_:
+            result = GREAT
+        else:
+            self._h.solve(self.T, self.p, self.rho, float(deltaT) if scalar else deltaT, self._Y,
+                          RR=self._RR, Qdot=self._Qdot, cost=self.cpuTimes_, status=self.cellStatus_)
+            if (self.cellStatus_ != 0).any():
+                bad = int(np.count_nonzero(self.cellStatus_))
+                # the reference lets CVODE failures propagate as a fatal error
+                raise RuntimeError(f"dfChemistryModel::solve: integrator failed in {bad} cell(s)")
+            result = GREAT
+        return min(result, 2.0 * float(deltaT)) if scalar else result
+
+    def correctThermo(self):
+        """T from (he, p, Y) by Newton; psi and rho updated (dfChemistryModel.C:494-511)."""
+        T, psi, rho, _, _ = self._h.correct_thermo(self.he, self.p, self._Y, self.T)
+        self.T[:] = T
+        self.psi[:] = psi
+        self.rho[:] = rho
+
+    def updateEnergy(self):
+        self.he[:] = self._h.h_from_T(self.T, self._Y)
+
+    def calculateW(self):
+        self._wrate[:] = self._h.wdot(self.T, self.p, self._Y)
+
+    def counters(self):
+        return self._h.counters()

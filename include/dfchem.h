@@ -126,6 +126,11 @@ int dfchem_last_counters(dfchem_handle h, unsigned long long out[4]);
  * operations smaller than 1 % of the mean load are dropped as in the reference. */
 int dfchem_balance_plan(const double* loads, int n_ranks, double* send);
 
+/* Measurement helper: FP64 DFMA throughput of `device` in TFLOP/s (16 independent chains per
+ * thread, best of 4 timed launches).  It is the denominator bench.py reports "% of FP64 peak"
+ * against, because MEASURED_PEAKS.json carries no FP64 figure. */
+int dfchem_bench_fp64_peak(int device, double* tflops);
+
 const char* dfchem_version(void);
 
 #ifdef __cplusplus
