@@ -29,36 +29,35 @@ struct CoefTable {
         for (size_t i = 1; i < v.size(); ++i)
             if (v[i] == c) return (int)i;
         v.push_back(c);
-        if (v.size() > 255) throw std::runtime_error("tables: more than 255 distinct schedule coefficients");
+        if (v.size() > 128) throw std::runtime_error("tables: more than 128 distinct schedule coefficients");
         return (int)v.size() - 1;
     }
 };
 
 // Longest-processing-time bin packing of whole targets onto kTeam lanes; returns the
-// lane-interleaved program.
-std::vector<U2> pack_program(std::vector<GTarget> targets, CoefTable& ct, int& n_iter) {
+// lane-blocked program (see GatherProg).
+std::vector<uint32_t> pack_program(std::vector<GTarget> targets, CoefTable& ct, int& n_iter) {
     std::stable_sort(targets.begin(), targets.end(),
                      [](const GTarget& a, const GTarget& b) { return a.e.size() > b.e.size(); });
-    std::vector<std::vector<U2>> lane(kTeam);
+    std::vector<std::vector<uint32_t>> lane(kTeam);
     for (const GTarget& t : targets) {
         if (t.e.empty()) continue;
         int best = 0;
         for (int l = 1; l < kTeam; ++l)
             if (lane[l].size() < lane[best].size()) best = l;
+        if (t.dst < 0 || t.dst > 0xFFF) throw std::runtime_error("tables: gather destination out of range");
         for (size_t i = 0; i < t.e.size(); ++i) {
-            if (t.e[i].src < 0 || t.e[i].src > 0xFFFF) throw std::runtime_error("tables: gather source out of range");
-            U2 u;
-            u.x = (uint32_t)t.e[i].src | ((uint32_t)ct.id(t.e[i].coef) << 16) |
-                  ((i + 1 == t.e.size()) ? (1u << 24) : 0u);
-            u.y = (uint32_t)t.dst;
-            lane[best].push_back(u);
+            if (t.e[i].src < 0 || t.e[i].src > 0xFFF) throw std::runtime_error("tables: gather source out of range");
+            lane[best].push_back((uint32_t)t.e[i].src | ((uint32_t)ct.id(t.e[i].coef) << 12) |
+                                 ((i + 1 == t.e.size()) ? (1u << 19) : 0u) | ((uint32_t)t.dst << 20));
         }
     }
     n_iter = 0;
     for (auto& l : lane) n_iter = std::max<int>(n_iter, (int)l.size());
-    std::vector<U2> out((size_t)n_iter * kTeam, U2{0u, 0u});
+    n_iter = (n_iter + 3) & ~3;
+    std::vector<uint32_t> out((size_t)n_iter * kTeam, 0u);
     for (int l = 0; l < kTeam; ++l)
-        for (size_t i = 0; i < lane[l].size(); ++i) out[i * kTeam + l] = lane[l][i];
+        for (size_t i = 0; i < lane[l].size(); ++i) out[(i / 4) * 4 * kTeam + l * 4 + i % 4] = lane[l][i];
     return out;
 }
 
@@ -95,6 +94,7 @@ int choose_np(int NA) {
 
 DevMech HostTables::rebase(const void* base) const {
     DevMech d = layout;
+    d.hot_base = shift(d.hot_base, base);
     d.perm = shift(d.perm, base);
     d.W = shift(d.W, base);
     d.Tmid = shift(d.Tmid, base);
@@ -197,7 +197,13 @@ HostTables build_tables(const Mechanism& m) {
         t.dst = j * ldj + i;
         t.e.push_back({src, coef});
     };
-    for (int r = 0; r < R; ++r) {
+    // internal reaction order: falloff first, then three-body, then elementary, so that the
+    // expensive (log10/exp10) falloff path is confined to the first warp iterations
+    std::vector<int> rorder(R);
+    for (int r = 0; r < R; ++r) rorder[r] = r;
+    std::stable_sort(rorder.begin(), rorder.end(), [&](int a, int b) { return m.kind[a] > m.kind[b]; });
+    for (int rn = 0; rn < R; ++rn) {
+        const int r = rorder[rn];  // index into the Mechanism record; rn = internal index
         const int* ri = &m.r_idx[r * kMaxSide];
         const int* pi = &m.p_idx[r * kMaxSide];
         const double* rnu = &m.r_nu[r * kMaxSide];
@@ -257,9 +263,9 @@ HostTables build_tables(const Mechanism& m) {
             fall.insert(fall.end(), rec, rec + 8);
         }
         if (m.A[r] < 0) throw std::runtime_error("tables: negative pre-exponential factor");
-        arrh[(size_t)r * 3 + 0] = m.A[r] > 0 ? std::log(m.A[r]) : -INFINITY;
-        arrh[(size_t)r * 3 + 1] = m.b[r];
-        arrh[(size_t)r * 3 + 2] = m.Ta[r];
+        arrh[(size_t)rn * 3 + 0] = m.A[r] > 0 ? std::log(m.A[r]) : -INFINITY;
+        arrh[(size_t)rn * 3 + 1] = m.b[r];
+        arrh[(size_t)rn * 3 + 2] = m.Ta[r];
 
         // net stoichiometry (internal active indices)
         std::map<int, double> net;
@@ -268,7 +274,7 @@ HostTables build_tables(const Mechanism& m) {
             if (pi[j] >= 0) net[inv[pi[j]]] += pnu[j];
         }
         for (auto& kv : net)
-            if (kv.second != 0.0) wt[kv.first].e.push_back({r, kv.second});
+            if (kv.second != 0.0) wt[kv.first].e.push_back({rn, kv.second});
 
         // derivative slots + Jacobian entries
         const int dq_off = n_dq;
@@ -296,9 +302,8 @@ HostTables build_tables(const Mechanism& m) {
         d.y = pf[1] | (pf[2] << 8) | (flags << 16) | ((uint32_t)rx_mset[r] << 24);
         d.z = (uint32_t)fall_id | ((uint32_t)pow_id << 16);
         d.w = (uint32_t)dq_off;
-        rdesc[r] = d;
+        rdesc[rn] = d;
     }
-    if (n_dq > 0xFFFF || R > 0xFFFF) throw std::runtime_error("tables: mechanism too large for 16-bit gather sources");
 
     // ---- gather programs -------------------------------------------------------------------
     CoefTable ct;
@@ -324,15 +329,15 @@ HostTables build_tables(const Mechanism& m) {
         }
     }
     int itA = 0, itB = 0, itJ = 0;
-    std::vector<U2> progA = pack_program(partA, ct, itA);
+    std::vector<uint32_t> progA = pack_program(partA, ct, itA);
     // stage B: coefficient 0.0 entries must still store -> give them a real id
-    std::vector<U2> progB = pack_program(tgtB, ct, itB);
+    std::vector<uint32_t> progB = pack_program(tgtB, ct, itB);
     std::vector<GTarget> jtargets;
     for (auto& kv : jt) {
         jtargets.push_back(kv.second);
         ht.jac_entries += (int)kv.second.e.size();
     }
-    std::vector<U2> progJ = pack_program(jtargets, ct, itJ);
+    std::vector<uint32_t> progJ = pack_program(jtargets, ct, itJ);
 
     // ---- per-cell shared-memory layout (doubles; every offset even for 16-byte access) -----
     DevMech& L = ht.layout;
@@ -359,26 +364,30 @@ HostTables build_tables(const Mechanism& m) {
     // ---- blob ------------------------------------------------------------------------------
     Blob B;
     ht.perm = perm;
+    // hot prefix (staged in shared memory by the kernels)
+    L.rdesc = as_ptr<U4>(B.add(rdesc));
+    L.coef = as_ptr<double>(B.add(ct.v));
+    L.ms_dflt = as_ptr<double>(B.add(ms_dflt));
+    L.ms_val = as_ptr<double>(B.add(ms_val));
+    L.ms_ptr = as_ptr<int>(B.add(ms_ptr));
+    L.ms_idx = as_ptr<int>(B.add(ms_idx));
+    L.wdotA.n_iter = itA;
+    L.wdotA.ent = as_ptr<uint32_t>(B.add(progA));
+    L.wdotB.n_iter = itB;
+    L.wdotB.ent = as_ptr<uint32_t>(B.add(progB));
+    L.jac.n_iter = itJ;
+    L.jac.ent = as_ptr<uint32_t>(B.add(progJ));
+    L.hot_base = as_ptr<uint8_t>(0);
+    L.hot_bytes = (int)((B.b.size() + 15) & ~size_t(15));
+    // cold tables (read once per cell from global memory)
     L.perm = as_ptr<int>(B.add(perm));
     L.W = as_ptr<double>(B.add(W));
     L.Tmid = as_ptr<double>(B.add(Tmid));
     L.nasa = as_ptr<double>(B.add(nasa));
     L.hc = as_ptr<double>(B.add(hc));
-    L.rdesc = as_ptr<U4>(B.add(rdesc));
     L.arrh = as_ptr<double>(B.add(arrh));
     L.fall = as_ptr<double>(B.add(fall));
     L.powtab = as_ptr<double>(B.add(powtab));
-    L.ms_dflt = as_ptr<double>(B.add(ms_dflt));
-    L.ms_ptr = as_ptr<int>(B.add(ms_ptr));
-    L.ms_idx = as_ptr<int>(B.add(ms_idx));
-    L.ms_val = as_ptr<double>(B.add(ms_val));
-    L.coef = as_ptr<double>(B.add(ct.v));
-    L.wdotA.n_iter = itA;
-    L.wdotA.ent = as_ptr<U2>(B.add(progA));
-    L.wdotB.n_iter = itB;
-    L.wdotB.ent = as_ptr<U2>(B.add(progB));
-    L.jac.n_iter = itJ;
-    L.jac.ent = as_ptr<U2>(B.add(progJ));
     ht.blob = std::move(B.b);
     return ht;
 }

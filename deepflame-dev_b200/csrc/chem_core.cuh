@@ -36,6 +36,7 @@
 #define DFC_LR (*regs)
 #define DFC_LDG(p) __ldg(p)
 #define DFC_UNROLL _Pragma("unroll")
+#define DFC_NOINLINE __noinline__
 #else
 #define DFC_LANES_BEGIN for (int tl = 0; tl < ::dfchem::kTeam; ++tl) {
 #define DFC_LANES_END }
@@ -43,6 +44,7 @@
 #define DFC_LR (regs[tl])
 #define DFC_LDG(p) (*(p))
 #define DFC_UNROLL
+#define DFC_NOINLINE
 #endif
 
 namespace dfchem {
@@ -140,6 +142,23 @@ DFC_HD double nasa_s_R(const double* a, double T, double logT) {
            DFC_LDG(a + 6);
 }
 
+// DevMech whose hot tables point into a copy of the hot prefix at `nb` (shared memory)
+DFC_HD DevMech rebase_hot(const DevMech& m, const uint8_t* nb) {
+    DevMech r = m;
+    const uint8_t* ob = m.hot_base;
+    r.hot_base = nb;
+    r.rdesc = reinterpret_cast<const U4*>(nb + (reinterpret_cast<const uint8_t*>(m.rdesc) - ob));
+    r.coef = reinterpret_cast<const double*>(nb + (reinterpret_cast<const uint8_t*>(m.coef) - ob));
+    r.ms_dflt = reinterpret_cast<const double*>(nb + (reinterpret_cast<const uint8_t*>(m.ms_dflt) - ob));
+    r.ms_val = reinterpret_cast<const double*>(nb + (reinterpret_cast<const uint8_t*>(m.ms_val) - ob));
+    r.ms_ptr = reinterpret_cast<const int*>(nb + (reinterpret_cast<const uint8_t*>(m.ms_ptr) - ob));
+    r.ms_idx = reinterpret_cast<const int*>(nb + (reinterpret_cast<const uint8_t*>(m.ms_idx) - ob));
+    r.wdotA.ent = reinterpret_cast<const uint32_t*>(nb + (reinterpret_cast<const uint8_t*>(m.wdotA.ent) - ob));
+    r.wdotB.ent = reinterpret_cast<const uint32_t*>(nb + (reinterpret_cast<const uint8_t*>(m.wdotB.ent) - ob));
+    r.jac.ent = reinterpret_cast<const uint32_t*>(nb + (reinterpret_cast<const uint8_t*>(m.jac.ent) - ob));
+    return r;
+}
+
 // team-uniform sum of the 32 partials in red[]
 DFC_HD double team_sum(const double* red) {
     double s = 0.0;
@@ -168,9 +187,8 @@ DFC_HD void compute_msets(const DevMech& m, double* sm, const double* cx, int df
     const double ctot = team_sum(red);
     DFC_LANES_BEGIN
     for (int s = tl; s < m.n_msets; s += kTeam) {
-        double M = DFC_LDG(m.ms_dflt + s) * ctot;
-        for (int q = DFC_LDG(m.ms_ptr + s); q < DFC_LDG(m.ms_ptr + s + 1); ++q)
-            M += DFC_LDG(m.ms_val + q) * cx[DFC_LDG(m.ms_idx + q)];
+        double M = m.ms_dflt[s] * ctot;  // hot tables may live in shared memory: plain loads
+        for (int q = m.ms_ptr[s]; q < m.ms_ptr[s + 1]; ++q) M += m.ms_val[q] * cx[m.ms_idx[q]];
         sm[m.off_M + s] = M;
     }
     DFC_LANES_END
@@ -188,7 +206,7 @@ DFC_HD void eval_reactions(const DevMech& m, double* sm, const double* cx, int d
     DFC_LANES_BEGIN
     for (int r = tl; r < m.R; r += kTeam) {
 #ifdef __CUDA_ARCH__
-        const uint4 dd = __ldg(reinterpret_cast<const uint4*>(m.rdesc) + r);
+        const uint4 dd = *(reinterpret_cast<const uint4*>(m.rdesc) + r);
         const U4 d{dd.x, dd.y, dd.z, dd.w};
 #else
         const U4 d = m.rdesc[r];
@@ -252,7 +270,7 @@ DFC_HD void eval_reactions(const DevMech& m, double* sm, const double* cx, int d
                     const double den = nn - 0.14 * x;
                     const double f1 = x / den;
                     const double g = 1.0 / (1.0 + f1 * f1);
-                    F = pow(10.0, lf * g);
+                    F = exp10(lf * g);
                     if (JAC && pr > kSmall) dF_dpr = F * (-lf * 2.0 * f1 * g * g * (nn / (den * den))) / pr;
                 }
                 const double ip = 1.0 / (1.0 + pr);
@@ -284,24 +302,41 @@ DFC_HD void run_gather(const GatherProg& g, const double* coef, const double* sr
     (void)dfc_lane;
     DFC_LANES_BEGIN
     double acc = 0.0;
-    const U2* e = g.ent + tl;
-    for (int it = 0; it < g.n_iter; ++it, e += kTeam) {
+    const uint32_t* e = g.ent + tl * 4;
+    for (int it = 0; it < g.n_iter; it += 4, e += 4 * kTeam) {
+        // four entries per 16-byte load; all loads of the batch are issued before the FMA chain
 #ifdef __CUDA_ARCH__
-        const uint2 u = __ldg(reinterpret_cast<const uint2*>(e));
+        const uint4 uu = *reinterpret_cast<const uint4*>(e);
+        const uint32_t u[4] = {uu.x, uu.y, uu.z, uu.w};
 #else
-        const U2 u = *e;
+        const uint32_t u[4] = {e[0], e[1], e[2], e[3]};
 #endif
-        acc = fma(DFC_LDG(coef + ((u.x >> 16) & 0xFFu)), src[u.x & 0xFFFFu], acc);
-        if (u.x & (1u << 24)) {
-            dst[u.y] = acc;
-            acc = 0.0;
+        double cf[4], sv[4];
+        DFC_UNROLL
+        for (int b = 0; b < 4; ++b) {
+            cf[b] = coef[(u[b] >> 12) & 0x7Fu];
+            sv[b] = src[u[b] & 0xFFFu];
+        }
+        DFC_UNROLL
+        for (int b = 0; b < 4; ++b) {
+            acc = fma(cf[b], sv[b], acc);
+            if (u[b] & (1u << 19)) {
+                dst[u[b] >> 20] = acc;
+                acc = 0.0;
+            }
         }
     }
     DFC_LANES_END
 }
 
-// wdot_i (i < NA) at concentrations cx -> out[i]
-DFC_HD void eval_wdot(const DevMech& m, double* sm, const double* cx, double* out, int dfc_lane,
+// wdot_i (i < NA) at concentrations cx -> out[i].  Deliberately NOT inlined on the device: it is
+// called from seven sites per Rosenbrock step and the kernel must stay instruction-cache resident.
+#if defined(__CUDACC__)
+__host__ __device__ DFC_NOINLINE
+#else
+inline
+#endif
+void eval_wdot(const DevMech& m, double* sm, const double* cx, double* out, int dfc_lane,
                       bool jac) {
     compute_msets(m, sm, cx, dfc_lane);
     if (jac)

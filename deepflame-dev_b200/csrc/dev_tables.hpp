@@ -24,13 +24,14 @@ struct alignas(16) U4 {
     uint32_t x, y, z, w;
 };
 
-// Lane-interleaved "segmented gather" program: lane l executes entries ent[it*kTeam + l],
-// it = 0..n_iter-1:   acc += coef[e.coef_id] * src[e.src];  if (e.store) { dst[e.dst] = acc; acc = 0; }
-// Every destination is written by exactly one lane, so no atomics are needed.
-//   x = src (bits 0-15) | coef_id (bits 16-23) | store (bit 24);   y = dst
+// Lane-blocked "segmented gather" program.  Lane l executes, for it = 0..n_iter-1, the entry
+// ent[(it/4)*4*kTeam + l*4 + it%4] (four consecutive entries of a lane are one 16-byte load):
+//   acc += coef[e.coef] * src[e.src];  if (e.store) { dst[e.dst] = acc; acc = 0; }
+// Every destination is written by exactly one lane, so no atomics are needed.  n_iter % 4 == 0.
+//   bits 0-11 src | bits 12-18 coef id | bit 19 store | bits 20-31 dst
 struct GatherProg {
     int n_iter;
-    const U2* ent;
+    const uint32_t* ent;
 };
 
 // Reaction descriptor (16 B).  A side holds up to 3 concentration factors; an integer
@@ -51,6 +52,10 @@ struct DevMech {
     // per-cell shared-memory layout, offsets in doubles from the cell's base (all even)
     int off_c, off_cs, off_kf, off_rkc, off_k0, off_lfc, off_M, off_q, off_dq, off_J, off_vec,
         off_row, off_part, off_red, cell_doubles;
+    // hot tables (rdesc, coef, efficiency sets, gather programs) are one contiguous prefix of the
+    // table blob; the kernels stage it in shared memory once per CTA (rebase_hot)
+    const uint8_t* hot_base;
+    int hot_bytes;
     // species tables, internal order
     const int* perm;       // [N]
     const double* W;       // [N]

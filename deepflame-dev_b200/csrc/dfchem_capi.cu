@@ -45,7 +45,7 @@ struct dfchem_ctx {
     DevMech dm{};
     double rtol = 1e-9, atol = 1e-15;  // dfChemistryModel.C:57-58
     int max_steps = 20000;             // CVODE default used by ReactorNet
-    int sm_count = 0, solve_blocks_per_sm = 0, wdot_blocks_per_sm = 0;
+    int sm_count = 0, warps = 0;  // warps (= cells in flight) per persistent CTA
     cudaStream_t streams[kSlots] = {nullptr, nullptr};
     DevBuf slot_in[kSlots], slot_out[kSlots], scratch;
     unsigned int* d_queue = nullptr;          // kSlots + 1 counters (last: dev API)
@@ -68,33 +68,40 @@ int fail(dfchem_ctx* h, int code, const std::string& msg) {
             return fail(h, DFCHEM_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
+size_t smem_bytes(const dfchem_ctx* h) {
+    return (size_t)h->dm.hot_bytes + (size_t)h->warps * h->dm.cell_doubles * sizeof(double);
+}
+
 template <int NP, int NSLOT>
 cudaError_t configure_t(dfchem_ctx* h) {
-    const size_t smem = (size_t)h->dm.cell_doubles * sizeof(double);
-    cudaError_t e;
-    e = cudaFuncSetAttribute(solve_kernel<NP, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int max_optin = 0;
+    cudaError_t e = cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(solve_kernel<NP, NSLOT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    // persistent CTA, one per SM: as many warps (cells in flight) as shared memory allows
+    const size_t cell = (size_t)h->dm.cell_doubles * sizeof(double);
+    h->warps = (int)std::min<size_t>(kMaxWarps, ((size_t)max_optin - h->dm.hot_bytes) / cell);
+    if (h->warps < 1) return cudaErrorLaunchOutOfResources;
+    const size_t smem = smem_bytes(h);
+    e = cudaFuncSetAttribute(solve_kernel<NP, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(wdot_kernel<NP, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->solve_blocks_per_sm, solve_kernel<NP, NSLOT>, kTeam, smem);
+    int nb = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, solve_kernel<NP, NSLOT>, h->warps * kTeam, smem);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->wdot_blocks_per_sm, wdot_kernel<NP, NSLOT>, kTeam, smem);
+    return nb >= 1 ? cudaSuccess : cudaErrorLaunchOutOfResources;
 }
 
 template <int NP, int NSLOT>
 void launch_solve_t(dfchem_ctx* h, const SolveArgs& a, unsigned int* queue, cudaStream_t s) {
-    const size_t smem = (size_t)h->dm.cell_doubles * sizeof(double);
-    const int grid = std::max(1, std::min(h->sm_count * h->solve_blocks_per_sm, a.nC));
-    solve_kernel<NP, NSLOT><<<grid, kTeam, smem, s>>>(h->dm, a, queue, h->d_counters);
+    const int grid = std::max(1, std::min(h->sm_count, (a.nC + h->warps - 1) / h->warps));
+    solve_kernel<NP, NSLOT><<<grid, h->warps * kTeam, smem_bytes(h), s>>>(h->dm, a, queue, h->d_counters);
 }
 template <int NP, int NSLOT>
 void launch_wdot_t(dfchem_ctx* h, int nC, const double* T, const double* p, const double* Y, int ldY,
                    double* wr, int ldW, unsigned int* queue, cudaStream_t s) {
-    const size_t smem = (size_t)h->dm.cell_doubles * sizeof(double);
-    const int grid = std::max(1, std::min(h->sm_count * h->wdot_blocks_per_sm, nC));
-    wdot_kernel<NP, NSLOT><<<grid, kTeam, smem, s>>>(h->dm, nC, T, p, Y, ldY, wr, ldW, queue);
+    const int grid = std::max(1, std::min(h->sm_count, (nC + h->warps - 1) / h->warps));
+    wdot_kernel<NP, NSLOT><<<grid, h->warps * kTeam, smem_bytes(h), s>>>(h->dm, nC, T, p, Y, ldY, wr, ldW, queue);
 }
 
 int launch_solve(dfchem_ctx* h, const SolveArgs& a, int qslot, cudaStream_t s) {
@@ -151,7 +158,6 @@ int finish_create(dfchem_ctx* h, int device, dfchem_handle* out) {
     DFC_DISPATCH_NP(h->dm.NP, CALL)
 #undef CALL
     if (e != cudaSuccess) return bail("kernel configuration", e);
-    if (h->solve_blocks_per_sm < 1) return bail("kernel does not fit on an SM", cudaErrorLaunchOutOfResources);
     *out = h;
     return DFCHEM_OK;
 }

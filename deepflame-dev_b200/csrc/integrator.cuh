@@ -10,8 +10,65 @@ namespace dfchem {
 // row does  f = a_ik/a_kk;  a_i -= f * a_k  (with column k replaced by the running inverse
 // column, i.e. a_ik <- -f).  Pivot rows are NOT rescaled; each row remembers 1/pivot (invd) and
 // the scale is applied in the mat-vec (gj_apply), which keeps every lane on the same DFMA
-// stream.  No pivoting: the matrix is I/(h g) - J with h under error control; a breakdown shows
-// up as a non-finite error norm and the step is retried with a smaller h.
+// stream.
+// ROTATING COLUMN STORAGE: at step k register j holds logical column (k + j) mod NP, so the
+// pivot column is always register 0 and the step index never indexes the register file.  The
+// rotation costs nothing: the update a'_(j-1) = fma(-f, u_j, a_j) writes to the neighbouring
+// register.  That lets the k-loop stay a real loop (about 2 KB of SASS instead of NP unrolled
+// copies, which overflowed the instruction cache).  After exactly NP steps the rotation has
+// gone full circle; padding rows/columns NA <= r < NP are identity, so their steps are no-ops.
+// No pivoting: the matrix is I/(h g) - J with h under error control; a breakdown shows up as a
+// non-finite error norm and the step is retried with a smaller h.
+template <int NP, int NSLOT, int SK>
+DFC_HD void gj_steps(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* regs, int dfc_lane, int k_begin,
+                     int k_end) {
+    (void)dfc_lane;
+#ifdef __CUDA_ARCH__
+#pragma unroll 1
+#endif
+    for (int k = k_begin; k < k_end; ++k) {
+        const int lk = k - SK * kTeam;
+        double* rowb = sm + m.off_row + (k & 1) * NP;
+        DFC_LANES_BEGIN
+        if (tl == lk) {
+            DFC_UNROLL
+            for (int j = 0; j + 1 < NP; j += 2) st2(rowb + j, DFC_LR.a[SK][j], DFC_LR.a[SK][j + 1]);
+            if (NP & 1) rowb[NP - 1] = DFC_LR.a[SK][NP - 1];
+        }
+        DFC_LANES_END
+        DFC_LANES_BEGIN
+        const double p = 1.0 / rowb[0];
+        double f[NSLOT];
+        DFC_UNROLL
+        for (int s = 0; s < NSLOT; ++s) {
+            const bool own = (s == SK) && (tl == lk);
+            f[s] = own ? 0.0 : DFC_LR.a[s][0] * p;
+            if (own) DFC_LR.invd[s] = p;
+        }
+        DFC_UNROLL
+        for (int j = 0; j < NP; j += 2) {
+            if (j + 1 < NP) {
+                const D2 u = ld2(rowb + j);
+                DFC_UNROLL
+                for (int s = 0; s < NSLOT; ++s) {
+                    if (j > 0) DFC_LR.a[s][j - 1] = fma(-f[s], u.x, DFC_LR.a[s][j]);
+                    DFC_LR.a[s][j] = fma(-f[s], u.y, DFC_LR.a[s][j + 1]);
+                }
+            } else {
+                const double u = rowb[j];
+                DFC_UNROLL
+                for (int s = 0; s < NSLOT; ++s) DFC_LR.a[s][j - 1] = fma(-f[s], u, DFC_LR.a[s][j]);
+            }
+        }
+        DFC_UNROLL
+        for (int s = 0; s < NSLOT; ++s) {
+            const bool own = (s == SK) && (tl == lk);
+            DFC_LR.a[s][NP - 1] = own ? 1.0 : -f[s];
+        }
+        DFC_LANES_END_NOSYNC
+    }
+}
+
 template <int NP, int NSLOT>
 DFC_HD void gj_invert(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* regs, int dfc_lane,
                       double inv_hg) {
@@ -29,55 +86,13 @@ DFC_HD void gj_invert(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* regs, i
                 DFC_LR.a[s][j] = (j < NA) ? ((j == row ? inv_hg : 0.0) - J[j * ldj + row] - gs) : 0.0;
         } else {
             DFC_UNROLL
-            for (int j = 0; j < NP; ++j) DFC_LR.a[s][j] = 0.0;
+            for (int j = 0; j < NP; ++j) DFC_LR.a[s][j] = (j == row) ? 1.0 : 0.0;  // identity padding
         }
         DFC_LR.invd[s] = 0.0;
     }
     DFC_LANES_END
-    DFC_UNROLL
-    for (int k = 0; k < NP; ++k) {
-        if (k < NA) {
-            const int sk = k / kTeam, lk = k % kTeam;
-            double* rowb = sm + m.off_row + (k & 1) * NP;
-            DFC_LANES_BEGIN
-            if (tl == lk) {
-                DFC_UNROLL
-                for (int j = 0; j + 1 < NP; j += 2) st2(rowb + j, DFC_LR.a[sk][j], DFC_LR.a[sk][j + 1]);
-                if (NP & 1) rowb[NP - 1] = DFC_LR.a[sk][NP - 1];
-            }
-            DFC_LANES_END
-            DFC_LANES_BEGIN
-            const double p = 1.0 / rowb[k];
-            double f[NSLOT];
-            DFC_UNROLL
-            for (int s = 0; s < NSLOT; ++s) {
-                const bool own = (s == sk) && (tl == lk);
-                f[s] = own ? 0.0 : DFC_LR.a[s][k] * p;
-                if (own) DFC_LR.invd[s] = p;
-            }
-            DFC_UNROLL
-            for (int j = 0; j + 1 < NP; j += 2) {
-                const D2 u = ld2(rowb + j);
-                DFC_UNROLL
-                for (int s = 0; s < NSLOT; ++s) {
-                    if (j != k) DFC_LR.a[s][j] = fma(-f[s], u.x, DFC_LR.a[s][j]);
-                    if (j + 1 != k) DFC_LR.a[s][j + 1] = fma(-f[s], u.y, DFC_LR.a[s][j + 1]);
-                }
-            }
-            if (NP & 1) {
-                const double u = rowb[NP - 1];
-                DFC_UNROLL
-                for (int s = 0; s < NSLOT; ++s)
-                    if (NP - 1 != k) DFC_LR.a[s][NP - 1] = fma(-f[s], u, DFC_LR.a[s][NP - 1]);
-            }
-            DFC_UNROLL
-            for (int s = 0; s < NSLOT; ++s) {
-                const bool own = (s == sk) && (tl == lk);
-                DFC_LR.a[s][k] = own ? 1.0 : -f[s];
-            }
-            DFC_LANES_END_NOSYNC
-        }
-    }
+    gj_steps<NP, NSLOT, 0>(m, sm, regs, dfc_lane, 0, NP < kTeam ? NP : kTeam);
+    if (NSLOT > 1) gj_steps<NP, NSLOT, (NSLOT > 1 ? 1 : 0)>(m, sm, regs, dfc_lane, kTeam, NP);
 }
 
 // x = A^-1 b for this lane's rows; b is read (broadcast) from shared memory vec[0..NP)

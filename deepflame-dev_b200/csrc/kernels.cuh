@@ -7,13 +7,27 @@
 
 namespace dfchem {
 
+// Shared memory of a CTA: [hot tables (m.hot_bytes)] [one cell block per warp (m.cell_doubles)].
+// The CTA is persistent (one per SM); its warps are independent after the table staging.
+constexpr int kMaxWarps = 8;
+
+__device__ __forceinline__ DevMech stage_hot_tables(const DevMech& m, unsigned char* smem) {
+    const uint4* src = reinterpret_cast<const uint4*>(m.hot_base);
+    uint4* dst = reinterpret_cast<uint4*>(smem);
+    for (int i = threadIdx.x; i < m.hot_bytes / 16; i += blockDim.x) dst[i] = __ldg(src + i);
+    __syncthreads();
+    return rebase_hot(m, smem);
+}
+
 // counters[0] accepted steps, [1] rejected steps, [2] failed cells
 template <int NP, int NSLOT>
-__global__ void __launch_bounds__(kTeam)
-solve_kernel(const DevMech m, const SolveArgs a, unsigned int* queue, unsigned long long* counters) {
+__global__ void __launch_bounds__(kMaxWarps* kTeam, 1)
+solve_kernel(const DevMech mg, const SolveArgs a, unsigned int* queue, unsigned long long* counters) {
     extern __shared__ double2 dfc_smem[];
-    double* sm = reinterpret_cast<double*>(dfc_smem);
-    const int lane = threadIdx.x;
+    unsigned char* smem = reinterpret_cast<unsigned char*>(dfc_smem);
+    const DevMech m = stage_hot_tables(mg, smem);
+    const int lane = threadIdx.x % kTeam, warp = threadIdx.x / kTeam;
+    double* sm = reinterpret_cast<double*>(smem + m.hot_bytes) + (size_t)warp * m.cell_doubles;
     LaneRegs<NP, NSLOT> regs;
     // Jacobian entries that no reaction touches stay zero for the whole launch
     for (int i = lane; i < (m.NA + 1) * m.ldj; i += kTeam) sm[m.off_J + i] = 0.0;
@@ -39,12 +53,14 @@ solve_kernel(const DevMech m, const SolveArgs a, unsigned int* queue, unsigned l
 }
 
 template <int NP, int NSLOT>
-__global__ void __launch_bounds__(kTeam)
-wdot_kernel(const DevMech m, int nC, const double* T, const double* p, const double* Y, int ldY,
+__global__ void __launch_bounds__(kMaxWarps* kTeam, 1)
+wdot_kernel(const DevMech mg, int nC, const double* T, const double* p, const double* Y, int ldY,
             double* wr, int ldW, unsigned int* queue) {
     extern __shared__ double2 dfc_smem[];
-    double* sm = reinterpret_cast<double*>(dfc_smem);
-    const int lane = threadIdx.x;
+    unsigned char* smem = reinterpret_cast<unsigned char*>(dfc_smem);
+    const DevMech m = stage_hot_tables(mg, smem);
+    const int lane = threadIdx.x % kTeam, warp = threadIdx.x / kTeam;
+    double* sm = reinterpret_cast<double*>(smem + m.hot_bytes) + (size_t)warp * m.cell_doubles;
     LaneRegs<NP, NSLOT> regs;
     while (true) {
         int cell = 0;
