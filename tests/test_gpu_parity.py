@@ -1,0 +1,175 @@
+"""GPU parity tests proper: every call goes through the C ABI of libdfchem_b200.so on cuda:0 and
+is compared with the oracle / golden vectors (tolerances: DESIGN.md 'Parity'), then with
+size-independent properties at full batch sizes.  Run on the B200 box: pytest -m gpu."""
+import ctypes
+
+import numpy as np
+import pytest
+from conftest import golden, rr_parity_error
+
+pytestmark = pytest.mark.gpu
+
+MECHS = ["es80", "h2_li", "drm19", "gri30", "c7_onestep", "ethanol66"]
+
+
+@pytest.fixture(scope="module")
+def handles(built):
+    import dfchem_host
+    from dfchem_host import synth
+
+    cache = {}
+
+    def get(name):
+        if name not in cache:
+            cache[name] = dfchem_host.Handle(synth.load_blob(name), 0)
+        return cache[name]
+
+    yield get
+    for h in cache.values():
+        h.close()
+
+
+def oracle_mech(name):
+    from dfchem_host import synth
+    from oracle import mech as OM
+
+    return OM.deserialize(synth.load_blob(name))
+
+
+def solve_golden(h, g, rtol, atol):
+    n = g["T"].shape[0]
+    h.set_tolerances(rtol, atol)
+    cost, st = np.zeros(n), np.zeros(n, np.int32)
+    RR, Q = h.solve(np.ascontiguousarray(g["T"]), np.ascontiguousarray(g["p"]), np.ascontiguousarray(g["rho"]),
+                    np.ascontiguousarray(g["dt"]), np.ascontiguousarray(g["Y"]), cost=cost, status=st)
+    return RR, Q, cost, st
+
+
+@pytest.mark.parametrize("name", MECHS)
+def test_wdot_matches_golden(handles, name):
+    g = golden(name)
+    h = handles(name)
+    assert h.species == [str(s) for s in g["species"]]
+    wr = h.wdot(np.ascontiguousarray(g["T"]), np.ascontiguousarray(g["p"]), np.ascontiguousarray(g["Y"]))
+    scale = np.abs(g["wrate"]).max(0, keepdims=True) + 1e-300
+    assert (np.abs(wr - g["wrate"]) / scale).max() < 1e-11
+
+
+@pytest.mark.parametrize("name", MECHS)
+def test_solve_parity_with_golden(handles, name):
+    g = golden(name)
+    h = handles(name)
+    RR, Q, cost, st = solve_golden(h, g, 1e-11, 1e-20)
+    assert (st == 0).all()
+    err = rr_parity_error(RR, g["RR"], g["Y"], g["rho"], g["dt"])
+    assert err.max() <= 1.0, (name, float(err.max()), np.unravel_index(err.argmax(), err.shape))
+    hc = h.hc
+    qscale = (np.abs(hc)[:, None] * (1e-6 * np.abs(g["RR"]) +
+                                     (g["rho"] / g["dt"])[None] * (1e-9 * np.abs(g["Y"]) + 1e-15))).sum(0)
+    assert (np.abs(Q - g["Qdot"]) <= qscale).all()
+    assert np.allclose(Q, -(hc[:, None] * RR).sum(0), rtol=1e-10, atol=1e-6 * np.abs(Q).max())
+    c = h.counters()
+    assert c["failed"] == 0 and c["accepted"] + c["rejected"] == int(cost.sum()) and c["launches"] >= 1
+
+
+def test_reference_tolerances_stay_close(handles):
+    g = golden("gri30")
+    RR, Q, cost, st = solve_golden(handles("gri30"), g, 1e-6, 1e-10)
+    assert (st == 0).all()
+    bound = 50.0 * (g["rho"] / g["dt"])[None] * (1e-6 * np.abs(g["Y"]) + 1e-10)
+    assert (np.abs(RR - g["RR"]) <= bound).all()
+
+
+@pytest.mark.parametrize("name", MECHS)
+def test_thermo_matches_oracle(handles, name):
+    from oracle import kinetics as K
+
+    g = golden(name)
+    h = handles(name)
+    m = oracle_mech(name)
+    Y = np.ascontiguousarray(g["Y"])
+    T = np.ascontiguousarray(g["T"])
+    he = h.h_from_T(T, Y)
+    assert np.allclose(he, g["he"], rtol=1e-13, atol=1e-6)
+    T2, psi, rho, cp, hai = h.correct_thermo(he, np.ascontiguousarray(g["p"]), Y, T + 150.0, want_cp=True,
+                                             want_hai=True)
+    assert np.abs(T2 - T).max() < 1e-7
+    Yn = (Y / Y.sum(0, keepdims=True)).T
+    assert np.allclose(psi, K.mean_W(m, Yn) / (8314.46261815324 * T2), rtol=1e-12)
+    assert np.allclose(rho, g["p"] * psi, rtol=1e-14)
+    assert np.allclose(cp, g["cp"], rtol=1e-9)
+    href = (K.h_RT(m, T2) * 8314.46261815324 * T2[:, None] / m.W[None]).T
+    assert np.allclose(hai, href, rtol=1e-10, atol=1e-3)
+
+
+def test_edge_cases(handles):
+    h = handles("h2_li")
+    g = golden("h2_li")
+    N = h.N
+    T, p, rho, Y = (np.ascontiguousarray(g[k]) for k in ("T", "p", "rho", "Y"))
+    h.set_tolerances(1e-10, 1e-18)
+    # empty batch
+    RR, Q = h.solve(T[:0], p[:0], rho[:0], 1e-6, np.zeros((N, 0)))
+    assert RR.shape == (N, 0) and Q.shape == (0,)
+    # single cell, ragged leading dimension (ld > nC) == slice of the full batch
+    full, _ = h.solve(T, p, rho, 1e-6, Y)
+    Ypad = np.zeros((N, 40))
+    Ypad[:, :5] = Y[:, :5]
+    RRpad = np.full((N, 64), np.nan)
+    st = np.zeros(5, np.int32)
+    q5 = np.zeros(5)
+    h.check(h.lib.dfchem_solve(h.h, 5, T.ctypes.data, p.ctypes.data, rho.ctypes.data, None, 1e-6,
+                               Ypad.ctypes.data, 40, RRpad.ctypes.data, 64, q5.ctypes.data, None,
+                               st.ctypes.data))
+    assert np.array_equal(RRpad[:, :5], full[:, :5]) and np.isnan(RRpad[:, 5:]).all()
+    one, _ = h.solve(T[:1].copy(), p[:1].copy(), rho[:1].copy(), 1e-6, np.ascontiguousarray(Y[:, :1]))
+    assert np.array_equal(one[:, 0], full[:, 0])
+    # uniform dt == per-cell dt field with the same value; results are deterministic
+    fld, _ = h.solve(T, p, rho, np.full(T.shape[0], 1e-6), Y)
+    assert np.array_equal(fld, full)
+    # dt = 0: no integration, RR = 0
+    z, qz = h.solve(T, p, rho, 0.0, Y)
+    assert np.all(z == 0) and np.all(qz == 0)
+    # normalisation quirk (dfChemistryModel.C:752-770): RR is taken against the raw Y
+    Ys = Y * 1.01
+    sc, _ = h.solve(T, p, rho, 1e-6, np.ascontiguousarray(Ys))
+    expect = full + (Y - Ys) / 1e-6 * rho[None]
+    assert np.allclose(sc, expect, rtol=1e-9, atol=1e-9 * np.abs(expect).max())
+    # step budget exhausted -> per-cell status 1, finite output
+    h.lib.dfchem_set_max_steps(h.h, 2)
+    st = np.zeros(T.shape[0], np.int32)
+    RRm, _ = h.solve(T, p, rho, 1e-6, Y, status=st)
+    h.lib.dfchem_set_max_steps(h.h, 20000)
+    assert (st == 1).any() and set(st) <= {0, 1} and np.isfinite(RRm).all()
+    # bad arguments
+    assert h.lib.dfchem_solve(h.h, 4, T.ctypes.data, p.ctypes.data, rho.ctypes.data, None, 1e-6, Y.ctypes.data, 2,
+                              full.ctypes.data, 4, qz.ctypes.data, None, None) == -1
+    assert b"bad argument" in h.lib.dfchem_last_error(h.h)
+
+
+def test_yaml_front_end_on_device(handles, tmp_path):
+    """dfchem_create straight from a Cantera-YAML file (the CanteraMixture role) vs the oracle."""
+    import dfchem_host
+    from test_mechanism_compiler import TINY
+
+    from oracle import kinetics as K
+    from oracle import mech as OM
+
+    y = tmp_path / "tiny.yaml"
+    y.write_text(TINY)
+    h = dfchem_host.Handle(str(y), 0)
+    m = OM.load_mechanism(str(y))
+    assert h.species == m.species and h.R == m.R and np.array_equal(h.W, m.W)
+    rng = np.random.default_rng(5)
+    n = 64
+    Y = rng.uniform(0.01, 1.0, (n, m.N))
+    Y /= Y.sum(1, keepdims=True)
+    T = rng.uniform(600.0, 2800.0, n)
+    p = rng.uniform(0.5, 20.0, n) * 101325.0
+    rho = K.density(m, T, p, Y)
+    ref = (K.wdot(m, K.RateConstants(m, T), rho[:, None] * Y / m.W[None]) * m.W[None]).T
+    wr = h.wdot(T, p, np.ascontiguousarray(Y.T))
+    assert (np.abs(wr - ref) / np.abs(ref).max(0, keepdims=True)).max() < 1e-11
+    h.close()
+    with pytest.raises(dfchem_host.DfchemError):
+        dfchem_host.Handle(str(tmp_path / "missing.yaml"), 0)
