@@ -1,0 +1,315 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: cell-chemistry integrations/s (BASELINE.json metric).
+
+A "step" is one chemistry sub-step (dfChemistryModel::solve(deltaT), deltaT = 1e-6 s) over one
+synthetic batch: by default the CH4 / GRI-3.0-class mechanism (mechanisms/CH4/gri30.yaml, 36
+species, 219 reactions), 4,194,304 cells PER GPU (weak scaling: each rank owns its own batch, the
+way each MPI rank owns its mesh partition in the reference; no data-path collective), at the
+tolerances of 35 of the reference's 38 cases (rtol 1e-6, atol 1e-10).
+
+  python bench.py --gpus N --steps K --warmup W            our arm  (torchrun for N > 1)
+  python bench.py --impl reference ...                     the reference's CPU algorithm
+                                                            (oracle/c port; rank 0 only)
+One JSON line on stdout (rank 0).  See DESIGN.md 'Measurement' for every field.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "deepflame-dev_b200"))
+
+METRIC = "cell-chemistry integrations/s"
+UNIT = "cells/s"
+
+# Algorithmic FP64 work per unit (flops: FMA = 2, exp/log/pow = 1), dense N x N
+# Jacobian / LU model with N = species that the ODE actually moves.  Keys: per-cell set-up,
+# per RHS evaluation, per analytic Jacobian, per (I/(h g) - J) formation, per LU (2/3 N^3),
+# per triangular solve pair (2 N^2).
+FLOP_MODEL = {
+    "gri30": dict(setup=3612 + 524, rhs=3807 + 50, jac=15453, form=2 * 36 * 36, lu=2 * 36 ** 3 // 3, solve=2 * 36 * 36),
+    "drm19": dict(setup=1598 + 201, rhs=1478 + 16, jac=4924, form=882, lu=6174, solve=882),
+    "es80": dict(setup=306 + 17, rhs=173, jac=552, form=98, lu=229, solve=98),
+    "h2_li": dict(setup=512 + 51, rhs=354 + 4, jac=1018, form=162, lu=486, solve=162),
+    "c7_onestep": dict(setup=156 + 2, rhs=36, jac=46, form=50, lu=83, solve=50),
+}
+STAGES = 6  # RODAS4: per step attempt 1 LU + 6 RHS + 6 solves; per accepted step 1 Jacobian
+
+
+def algorithmic_flops(mech, n_cells, accepted, rejected):
+    f = FLOP_MODEL[mech]
+    attempts = accepted + rejected
+    return (n_cells * f["setup"] + attempts * (STAGES * f["rhs"] + f["form"] + f["lu"] + STAGES * f["solve"])
+            + accepted * f["jac"])
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        busy = [s for s in sm if s > 0]
+        return {"sm_mhz": float(np.median(busy)) if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def load_oracle_c():
+    lib = ctypes.CDLL(os.path.join(ROOT, "oracle", "c", "liboracle_c.so"))
+    lib.oc_load.restype = ctypes.c_void_p
+    lib.oc_load.argtypes = [ctypes.c_char_p, ctypes.c_size_t]
+    return lib
+
+
+def cpu_reference_rate(mech, batch, n_sample, rtol, atol, dt, threads):
+    """Times the reference's CPU algorithm (oracle/c: per-cell variable-order BDF + Newton + dense
+    LU + finite-difference Jacobian, fresh per cell, one cell per task on `threads` host threads)
+    on the first n_sample cells of the batch.  Returns (cells/s, seconds, mean BDF steps/cell)."""
+    from dfchem_host import synth
+
+    lib = load_oracle_c()
+    blob = synth.load_blob(mech)
+    m = ctypes.c_void_p(lib.oc_load(blob, len(blob)))
+    P = ctypes.POINTER(ctypes.c_double)
+    n = n_sample
+    T, p, rho = (np.ascontiguousarray(batch[k][:n]) for k in ("T", "p", "rho"))
+    Y = np.ascontiguousarray(batch["Y"][:, :n])
+    N = Y.shape[0]
+    RR, Q = np.empty((N, n)), np.empty(n)
+    stats = (ctypes.c_long * 3)()
+    t0 = time.perf_counter()
+    lib.oc_solve_batch(m, n, T.ctypes.data_as(P), p.ctypes.data_as(P), rho.ctypes.data_as(P), None,
+                       ctypes.c_double(dt), Y.ctypes.data_as(P), n, ctypes.c_double(rtol), ctypes.c_double(atol),
+                       20000, RR.ctypes.data_as(P), n, Q.ctypes.data_as(P), None, None, threads, stats)
+    el = time.perf_counter() - t0
+    lib.oc_free(m)
+    return n / el, el, stats[0] / n
+
+
+def run_reference(args, rank):
+    """--impl reference: the reference's own CPU algorithm for the path on the box's host cores
+    (Cantera/CVODE are absent, so this is the oracle/c port; DESIGN.md 'CPU baseline')."""
+    if rank != 0:
+        return
+    from dfchem_host import synth
+    from oracle import mech as OM
+
+    m = OM.deserialize(synth.load_blob(args.mech))
+    threads = os.cpu_count() or 1
+    sample = args.ref_cells or 64 * threads
+    batch = synth.make_batch(args.mech, m.species, m.W, sample, seed=12345)
+    times = []
+    for i in range(args.warmup + args.steps):
+        rate, el, steps = cpu_reference_rate(args.mech, batch, sample, args.rtol, args.atol, args.dt, threads)
+        if i >= args.warmup:
+            times.append(el)
+    ms = 1e3 * float(np.mean(times))
+    value = sample / (ms * 1e-3)
+    desc = f"first {sample} cells of the seed-12345 batch per step ({steps:.1f} BDF steps/cell)"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, args.cells),   # same workload; each step times a bounded sample of it
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+def workload_config(args, cells):
+    return {"workload": f"{args.mech} ({'mechanisms/CH4/gri30.yaml, 36 species / 219 reactions' if args.mech == 'gri30' else args.mech}), "
+                        f"{cells} synthetic cells per GPU, T~U[300,2500] K, p~U[1,10] atm, 50% fuel/air phi~U[0.5,2] + 50% "
+                        f"ignition-trajectory states, deltaT={args.dt:g} s",
+            "cells_per_gpu": cells, "rtol": args.rtol, "atol": args.atol, "integrator": "RODAS4 (Rosenbrock 4(3), 6 stages)",
+            "l2": "inputs (T,p,rho,Y = 1.3 GB at 4M cells) exceed the 126 MB L2; no explicit flush"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mech", default="gri30")
+    ap.add_argument("--cells", type=int, default=4194304)
+    ap.add_argument("--rtol", type=float, default=1e-6)
+    ap.add_argument("--atol", type=float, default=1e-10)
+    ap.add_argument("--dt", type=float, default=1e-6)
+    ap.add_argument("--ref-cells", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    import dfchem_host
+    from dfchem_host import synth
+
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = dfchem_host.load_library()   # raises if the CUDA library is missing: no fallback
+    h = dfchem_host.Handle(synth.load_blob(args.mech), local)
+    h.set_tolerances(args.rtol, args.atol)
+    n = args.cells
+    batch = synth.make_batch(args.mech, h.species, h.W, n, seed=12345 + rank)
+    N = h.N
+
+    # ---- device-resident arm -------------------------------------------------------------
+    d = {k: torch.from_numpy(v).to(dev) for k, v in batch.items()}
+    dRR = torch.empty((N, n), dtype=torch.float64, device=dev)
+    dQ = torch.empty(n, dtype=torch.float64, device=dev)
+    dcost = torch.empty(n, dtype=torch.float64, device=dev)
+    dstat = torch.empty(n, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream()
+
+    def step_dev():
+        h.check(lib.dfchem_solve_dev(h.h, n, d["T"].data_ptr(), d["p"].data_ptr(), d["rho"].data_ptr(), None, args.dt,
+                                     d["Y"].data_ptr(), n, dRR.data_ptr(), n, dQ.data_ptr(), dcost.data_ptr(),
+                                     dstat.data_ptr(), stream.cuda_stream))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(args.warmup):
+        step_dev()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_dev()
+    e1.record(stream)
+    barrier()
+    ms_local = e0.elapsed_time(e1) / args.steps
+    ms = max_over_ranks(ms_local)
+    clocks = sampler.stop() if rank == 0 else None
+    cnt = h.counters()
+    failed = int((dstat != 0).sum().item())
+    cost_mean = float(dcost.mean().item())
+    cost_max = float(dcost.max().item())
+    value = world * n / (ms * 1e-3)
+
+    # ---- end-to-end arm: host buffers through the C ABI, copies inside the timed region --------
+    pin = {k: torch.from_numpy(v).pin_memory() for k, v in batch.items()}
+    hRR = torch.empty((N, n), dtype=torch.float64).pin_memory()
+    hQ = torch.empty(n, dtype=torch.float64).pin_memory()
+
+    def step_host():
+        h.check(lib.dfchem_solve(h.h, n, pin["T"].data_ptr(), pin["p"].data_ptr(), pin["rho"].data_ptr(), None, args.dt,
+                                 pin["Y"].data_ptr(), n, hRR.data_ptr(), n, hQ.data_ptr(), None, None))
+
+    step_host()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_host()
+    torch.cuda.synchronize()
+    e2e_ms = max_over_ranks(1e3 * (time.perf_counter() - t0) / args.steps)
+    barrier()
+    same = bool(torch.equal(hRR, dRR.cpu()))
+    e2e = {"value": world * n / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
+           "h2d_bytes_per_step": (N + 3) * n * 8, "d2h_bytes_per_step": (N + 1) * n * 8,
+           "matches_device_arm": same}
+
+    if rank == 0:
+        pk = ctypes.c_double()
+        rc = lib.dfchem_bench_fp64_peak(local, ctypes.byref(pk))
+        peak = pk.value if rc == 0 else None
+        flops = algorithmic_flops(args.mech, n, cnt["accepted"], cnt["rejected"]) if args.mech in FLOP_MODEL else None
+        achieved = flops / (ms_local * 1e-3) / 1e12 if flops else None
+        traffic = None
+        tfile = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tfile):
+            try:
+                traffic = json.load(open(tfile)).get(args.mech)
+            except (OSError, ValueError):
+                traffic = None
+        roof = {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                "frac": (achieved / peak) if (achieved and peak) else None, "traffic": traffic,
+                "peak_source": "dfchem_bench_fp64_peak (DFMA microbenchmark, measured in this run; MEASURED_PEAKS.json has no FP64 entry)",
+                "kernel": "solve_kernel", "algorithmic_flops_per_launch": flops,
+                "hbm_algorithmic_GBps": (2 * N + 6) * 8 * n / (ms_local * 1e-3) / 1e9,
+                "step_attempts_per_s": (cnt["accepted"] + cnt["rejected"]) / (ms_local * 1e-3)}
+        out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+               "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+               "data": "synthetic", "config": workload_config(args, n), "clocks": clocks, "e2e": e2e,
+               "gpu_launches": args.steps * 1, "roofline": roof,
+               "integrator_stats": {"accepted_steps": cnt["accepted"], "rejected_steps": cnt["rejected"],
+                                    "mean_attempts_per_cell": cost_mean, "max_attempts_per_cell": cost_max,
+                                    "failed_cells": failed}}
+        if world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            probe = min(n, 16 * threads)
+            r0, el0, _ = cpu_reference_rate(args.mech, batch, probe, args.rtol, args.atol, args.dt, threads)
+            sample = int(min(n, max(probe, r0 * 15.0)))
+            r1, el1, bsteps = cpu_reference_rate(args.mech, batch, sample, args.rtol, args.atol, args.dt, threads)
+            out["cpu_baseline"] = {"value": r1, "unit": UNIT, "cores": threads, "kind": "port",
+                                   "sample": f"first {sample} cells of the same batch, {el1:.1f} s, "
+                                             f"{bsteps:.1f} BDF steps/cell (oracle/c: CVODE-equivalent BDF + FD Jacobian + dense LU)"}
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

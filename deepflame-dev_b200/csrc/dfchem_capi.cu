@@ -81,10 +81,12 @@ cudaError_t configure_t(dfchem_ctx* h) {
     const size_t cell = (size_t)h->dm.cell_doubles * sizeof(double);
     h->warps = (int)std::min<size_t>(kMaxWarps, ((size_t)max_optin - h->dm.hot_bytes) / cell);
     if (h->warps < 1) return cudaErrorLaunchOutOfResources;
+    // the attribute is per kernel instantiation and shared by every handle using it: always the
+    // device maximum, never this handle's size
     const size_t smem = smem_bytes(h);
-    e = cudaFuncSetAttribute(solve_kernel<NP, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = cudaFuncSetAttribute(solve_kernel<NP, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(wdot_kernel<NP, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = cudaFuncSetAttribute(wdot_kernel<NP, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin);
     if (e != cudaSuccess) return e;
     int nb = 0;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, solve_kernel<NP, NSLOT>, h->warps * kTeam, smem);
