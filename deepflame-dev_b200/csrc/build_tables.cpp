@@ -34,31 +34,92 @@ struct CoefTable {
     }
 };
 
-// Longest-processing-time bin packing of whole targets onto kTeam lanes; returns the
-// lane-blocked program (see GatherProg).
-std::vector<uint32_t> pack_program(std::vector<GTarget> targets, CoefTable& ct, int& n_iter) {
-    std::stable_sort(targets.begin(), targets.end(),
-                     [](const GTarget& a, const GTarget& b) { return a.e.size() > b.e.size(); });
-    std::vector<std::vector<uint32_t>> lane(kTeam);
-    for (const GTarget& t : targets) {
-        if (t.e.empty()) continue;
-        int best = 0;
-        for (int l = 1; l < kTeam; ++l)
-            if (lane[l].size() < lane[best].size()) best = l;
-        if (t.dst < 0 || t.dst > 0xFFF) throw std::runtime_error("tables: gather destination out of range");
-        for (size_t i = 0; i < t.e.size(); ++i) {
-            if (t.e[i].src < 0 || t.e[i].src > 0xFFF) throw std::runtime_error("tables: gather source out of range");
-            lane[best].push_back((uint32_t)t.e[i].src | ((uint32_t)ct.id(t.e[i].coef) << 12) |
-                                 ((i + 1 == t.e.size()) ? (1u << 19) : 0u) | ((uint32_t)t.dst << 20));
+struct HostRowProg {
+    int nA = 0, nB = 0;
+    std::vector<U4> ent;
+    std::vector<uint32_t> dst;
+};
+
+// Rows of one target: type-A rows (+/-1 entries, integer coefficients expanded) then type-B rows.
+struct TargetRows {
+    int dst;
+    std::vector<U4> a, b;
+};
+
+TargetRows make_rows(const GTarget& t, CoefTable& ct, int zero_src) {
+    TargetRows tr;
+    tr.dst = t.dst;
+    std::vector<uint32_t> ea, eb;
+    for (const GEntry& e : t.e) {
+        if (e.src < 0 || e.src > 0x1FFF) throw std::runtime_error("tables: row-program source out of range");
+        const uint32_t off = (uint32_t)e.src * 8u;
+        const double ac = std::fabs(e.coef);
+        if (ac == std::round(ac) && ac >= 1.0 && ac <= 4.0 && zero_src >= 0) {
+            for (int k = 0; k < (int)ac; ++k) ea.push_back(off | (e.coef < 0 ? 0x80000000u : 0u));
+        } else if (e.coef != 0.0) {
+            eb.push_back(off | ((uint32_t)ct.id(e.coef) << 16));
         }
     }
-    n_iter = 0;
-    for (auto& l : lane) n_iter = std::max<int>(n_iter, (int)l.size());
-    n_iter = (n_iter + 3) & ~3;
-    std::vector<uint32_t> out((size_t)n_iter * kTeam, 0u);
-    for (int l = 0; l < kTeam; ++l)
-        for (size_t i = 0; i < lane[l].size(); ++i) out[(i / 4) * 4 * kTeam + l * 4 + i % 4] = lane[l][i];
-    return out;
+    auto rows = [](std::vector<uint32_t>& v, uint32_t pad, std::vector<U4>& out) {
+        while (v.size() % 4) v.push_back(pad);
+        for (size_t i = 0; i < v.size(); i += 4) out.push_back(U4{v[i], v[i + 1], v[i + 2], v[i + 3]});
+    };
+    rows(ea, zero_src >= 0 ? (uint32_t)zero_src * 8u : 0u, tr.a);
+    rows(eb, 0u, tr.b);
+    return tr;
+}
+
+// Whole targets onto kTeam lanes, longest first onto the least loaded lane (a type-B row costs
+// about 1.75 type-A rows).  All rows of a target stay on one lane: first row stores, rest add.
+HostRowProg pack_rows(std::vector<TargetRows> targets, int dst_limit) {
+    auto cost = [](const TargetRows& t) { return 4 * (int)t.a.size() + 7 * (int)t.b.size(); };
+    std::stable_sort(targets.begin(), targets.end(),
+                     [&](const TargetRows& x, const TargetRows& y) { return cost(x) > cost(y); });
+    struct Lane {
+        std::vector<U4> a, b;
+        std::vector<uint32_t> da, db;
+        int load = 0;
+    };
+    std::vector<Lane> lane(kTeam);
+    for (const TargetRows& t : targets) {
+        if (t.a.empty() && t.b.empty()) continue;
+        if (t.dst < 0 || t.dst >= dst_limit) throw std::runtime_error("tables: row-program destination out of range");
+        int best = 0;
+        for (int l = 1; l < kTeam; ++l)
+            if (lane[l].load < lane[best].load) best = l;
+        Lane& L = lane[best];
+        L.load += cost(t);
+        bool first = true;
+        for (const U4& r : t.a) {
+            L.a.push_back(r);
+            L.da.push_back((uint32_t)t.dst * 8u | (first ? 0u : kRowAcc));
+            first = false;
+        }
+        for (const U4& r : t.b) {
+            L.b.push_back(r);
+            L.db.push_back((uint32_t)t.dst * 8u | (first ? 0u : kRowAcc));
+            first = false;
+        }
+    }
+    HostRowProg p;
+    for (auto& L : lane) {
+        p.nA = std::max(p.nA, (int)L.a.size());
+        p.nB = std::max(p.nB, (int)L.b.size());
+    }
+    const int n = p.nA + p.nB;
+    p.ent.assign((size_t)std::max(n, 1) * kTeam, U4{0, 0, 0, 0});
+    p.dst.assign((size_t)std::max(n, 1) * kTeam, kRowSkip);
+    for (int l = 0; l < kTeam; ++l) {
+        for (size_t i = 0; i < lane[l].a.size(); ++i) {
+            p.ent[i * kTeam + l] = lane[l].a[i];
+            p.dst[i * kTeam + l] = lane[l].da[i];
+        }
+        for (size_t i = 0; i < lane[l].b.size(); ++i) {
+            p.ent[(p.nA + i) * kTeam + l] = lane[l].b[i];
+            p.dst[(p.nA + i) * kTeam + l] = lane[l].db[i];
+        }
+    }
+    return p;
 }
 
 bool is_int(double x) { return std::fabs(x - std::round(x)) < 1e-12; }
@@ -84,7 +145,7 @@ const T* shift(const T* off, const void* base) {
 }
 
 int choose_np(int NA) {
-    static const int sizes[] = {8, 16, 20, 24, 32, 34, 40, 48, 64};
+    static const int sizes[] = {8, 16, 20, 24, 32, 33, 34, 35, 36, 40, 48, 64};
     for (int s : sizes)
         if (NA <= s) return s;
     throw std::runtime_error("tables: more than 64 active species is not supported by the compiled kernel set");
@@ -104,14 +165,14 @@ DevMech HostTables::rebase(const void* base) const {
     d.arrh = shift(d.arrh, base);
     d.fall = shift(d.fall, base);
     d.powtab = shift(d.powtab, base);
-    d.ms_dflt = shift(d.ms_dflt, base);
-    d.ms_ptr = shift(d.ms_ptr, base);
-    d.ms_idx = shift(d.ms_idx, base);
-    d.ms_val = shift(d.ms_val, base);
     d.coef = shift(d.coef, base);
+    d.msets.ent = shift(d.msets.ent, base);
+    d.msets.dst = shift(d.msets.dst, base);
     d.wdotA.ent = shift(d.wdotA.ent, base);
-    d.wdotB.ent = shift(d.wdotB.ent, base);
+    d.wdotA.dst = shift(d.wdotA.dst, base);
+    d.wdotB = shift(d.wdotB, base);
     d.jac.ent = shift(d.jac.ent, base);
+    d.jac.dst = shift(d.jac.dst, base);
     return d;
 }
 
@@ -226,7 +287,8 @@ HostTables build_tables(const Mechanism& m) {
             }
         }
         if (nrf > 3 || npf > 3) fast = false;
-        uint8_t rf[3] = {255, 255, 255}, pf[3] = {255, 255, 255};
+        const uint8_t kNone = (uint8_t)N;  // slot N of the concentration arrays holds 1.0
+        uint8_t rf[3] = {kNone, kNone, kNone}, pf[3] = {kNone, kNone, kNone};
         uint32_t flags = (uint32_t)kind | (rev ? kFlagRev : 0u);
         int pow_id = 0;
         if (fast) {
@@ -280,9 +342,9 @@ HostTables build_tables(const Mechanism& m) {
         const int dq_off = n_dq;
         std::vector<std::pair<int, int>> deps;  // (species j, slot)
         for (int a = 0; a < 3; ++a)
-            if (rf[a] != 255) deps.push_back({rf[a], n_dq++});
+            if (rf[a] != kNone) deps.push_back({rf[a], n_dq++});
         for (int a = 0; a < 3; ++a)
-            if (pf[a] != 255) deps.push_back({pf[a], n_dq++});
+            if (pf[a] != kNone) deps.push_back({pf[a], n_dq++});
         int mslot = -1;
         if (kind != kElementary) mslot = n_dq++;
         for (auto& kv : net) {
@@ -298,46 +360,60 @@ HostTables build_tables(const Mechanism& m) {
             }
         }
         U4 d;
-        d.x = rf[0] | (rf[1] << 8) | (rf[2] << 16) | ((uint32_t)pf[0] << 24);
-        d.y = pf[1] | (pf[2] << 8) | (flags << 16) | ((uint32_t)rx_mset[r] << 24);
-        d.z = (uint32_t)fall_id | ((uint32_t)pow_id << 16);
+        if (fall_id > 0xFFF || pow_id > 0xFFF) throw std::runtime_error("tables: too many falloff / pow reactions");
+        d.x = flags | ((uint32_t)rf[0] << 3) | ((uint32_t)rf[1] << 11) | ((uint32_t)rf[2] << 19);
+        d.y = ((uint32_t)pf[0] << 3) | ((uint32_t)pf[1] << 11) | ((uint32_t)pf[2] << 19);
+        d.z = (uint32_t)rx_mset[r] | ((uint32_t)fall_id << 8) | ((uint32_t)pow_id << 20);
         d.w = (uint32_t)dq_off;
         rdesc[rn] = d;
     }
 
-    // ---- gather programs -------------------------------------------------------------------
+    // ---- row programs ----------------------------------------------------------------------
     CoefTable ct;
-    // wdot stage A: split each species' entries into chunks so lanes are balanced
-    int total = 0;
-    for (auto& t : wt) total += (int)t.e.size();
-    ht.wdot_entries = total;
-    const int chunk = std::max(4, (total + 2 * kTeam - 1) / (2 * kTeam));
-    std::vector<GTarget> partA, tgtB(NA);
+    // third-body sets: M_s = dflt_s * ctot + sum_j (eff_sj - dflt_s) c_j ; ctot lives in slot N+1
+    std::vector<TargetRows> mrows;
+    for (int sidx = 0; sidx < n_msets; ++sidx) {
+        GTarget t;
+        t.dst = sidx;
+        if (ms_dflt[sidx] != 0.0) t.e.push_back({N + 1, ms_dflt[sidx]});
+        for (int q = ms_ptr[sidx]; q < ms_ptr[sidx + 1]; ++q) t.e.push_back({ms_idx[q], ms_val[q]});
+        if (t.e.empty()) t.e.push_back({N + 1, 0.0});
+        mrows.push_back(make_rows(t, ct, -1));
+        if (mrows.back().b.empty()) mrows.back().b.push_back(U4{0, 0, 0, 0});  // M_s = 0 must still be stored
+    }
+    HostRowProg progM = pack_rows(mrows, std::max(n_msets, 1));
+    // wdot stage A: every row of a species is its own partial sum (rows spread evenly over the
+    // lanes); stage B adds each species' contiguous partials
+    std::vector<TargetRows> arows;
+    std::vector<uint32_t> wdotB(NP, 0u);
     int n_part = 0;
     for (int i = 0; i < NA; ++i) {
-        tgtB[i].dst = i;
-        for (size_t a = 0; a < wt[i].e.size(); a += chunk) {
-            GTarget p;
-            p.dst = n_part;
-            p.e.assign(wt[i].e.begin() + a, wt[i].e.begin() + std::min(wt[i].e.size(), a + chunk));
-            partA.push_back(p);
-            tgtB[i].e.push_back({n_part, 1.0});
-            ++n_part;
+        ht.wdot_entries += (int)wt[i].e.size();
+        GTarget t = wt[i];
+        TargetRows tr = make_rows(t, ct, R);
+        const int first = n_part;
+        for (const U4& r : tr.a) {
+            TargetRows one;
+            one.dst = n_part++;
+            one.a.push_back(r);
+            arows.push_back(one);
         }
-        if (tgtB[i].e.empty()) {  // active species with zero net production everywhere
-            tgtB[i].e.push_back({0, 0.0});
+        for (const U4& r : tr.b) {
+            TargetRows one;
+            one.dst = n_part++;
+            one.b.push_back(r);
+            arows.push_back(one);
         }
+        if (n_part - first > 0xFFFF || first > 0xFFFF) throw std::runtime_error("tables: too many wdot partial sums");
+        wdotB[i] = (uint32_t)first | ((uint32_t)(n_part - first) << 16);
     }
-    int itA = 0, itB = 0, itJ = 0;
-    std::vector<uint32_t> progA = pack_program(partA, ct, itA);
-    // stage B: coefficient 0.0 entries must still store -> give them a real id
-    std::vector<uint32_t> progB = pack_program(tgtB, ct, itB);
-    std::vector<GTarget> jtargets;
+    HostRowProg progA = pack_rows(arows, std::max(n_part, 1));
+    std::vector<TargetRows> jrows;
     for (auto& kv : jt) {
-        jtargets.push_back(kv.second);
         ht.jac_entries += (int)kv.second.e.size();
+        jrows.push_back(make_rows(kv.second, ct, n_dq));
     }
-    std::vector<uint32_t> progJ = pack_program(jtargets, ct, itJ);
+    HostRowProg progJ = pack_rows(jrows, (NA + 1) * ldj);
 
     // ---- per-cell shared-memory layout (doubles; every offset even for 16-byte access) -----
     DevMech& L = ht.layout;
@@ -345,20 +421,26 @@ HostTables build_tables(const Mechanism& m) {
     L.n_dq = n_dq; L.n_part = n_part; L.ldj = ldj;
     int off = 0;
     auto take = [&](int n) { int o = off; off += (n + 1) & ~1; return o; };
-    L.off_c = take(N);
-    L.off_cs = take(N);
-    L.off_kf = take(R);
-    L.off_rkc = take(R);
+    L.off_c = take(N + 2);
+    L.off_cs = take(N + 2);
+    L.off_kf = take(2 * R);
     L.off_k0 = take(n_fall);
     L.off_lfc = take(n_fall);
     L.off_M = take(n_msets);
-    L.off_q = take(R);
-    L.off_dq = take(std::max(n_dq, N));  // also used as g[N] scratch during set-up
+    L.off_q = take(R + 1);
+    // dq is dead once the Jacobian row program has run (inside eval_wdot<true>, before the wdot
+    // rows); the partial sums, the stage vector and the Gauss-Jordan pivot-row buffer reuse it
+    const int dq_need = std::max(n_dq + 1, N);
+    const int alias_need = ((std::max(n_part, 1) + 1) & ~1) + ((NP + 1) & ~1) + 2 * (NP + 6);  // row: 2 pivot records
+    L.off_dq = take(std::max(dq_need, alias_need));
+    {
+        int o = L.off_dq;
+        L.off_part = o; o += (std::max(n_part, 1) + 1) & ~1;
+        L.off_vec = o; o += (NP + 1) & ~1;
+        L.off_row = o;
+    }
     L.off_J = take((NA + 1) * ldj);
-    L.off_vec = take(NP);
-    L.off_row = take(2 * NP);
-    L.off_part = take(std::max(n_part, 1));
-    L.off_red = take(kTeam);
+    L.off_red = 0;  // unused (team sums go through warp shuffles)
     L.cell_doubles = off;
 
     // ---- blob ------------------------------------------------------------------------------
@@ -367,16 +449,16 @@ HostTables build_tables(const Mechanism& m) {
     // hot prefix (staged in shared memory by the kernels)
     L.rdesc = as_ptr<U4>(B.add(rdesc));
     L.coef = as_ptr<double>(B.add(ct.v));
-    L.ms_dflt = as_ptr<double>(B.add(ms_dflt));
-    L.ms_val = as_ptr<double>(B.add(ms_val));
-    L.ms_ptr = as_ptr<int>(B.add(ms_ptr));
-    L.ms_idx = as_ptr<int>(B.add(ms_idx));
-    L.wdotA.n_iter = itA;
-    L.wdotA.ent = as_ptr<uint32_t>(B.add(progA));
-    L.wdotB.n_iter = itB;
-    L.wdotB.ent = as_ptr<uint32_t>(B.add(progB));
-    L.jac.n_iter = itJ;
-    L.jac.ent = as_ptr<uint32_t>(B.add(progJ));
+    auto add_prog = [&](const HostRowProg& hp, RowProg& out) {
+        out.nA = hp.nA;
+        out.nB = hp.nB;
+        out.ent = as_ptr<U4>(B.add(hp.ent));
+        out.dst = as_ptr<uint32_t>(B.add(hp.dst));
+    };
+    add_prog(progM, L.msets);
+    add_prog(progA, L.wdotA);
+    L.wdotB = as_ptr<uint32_t>(B.add(wdotB));
+    add_prog(progJ, L.jac);
     L.hot_base = as_ptr<uint8_t>(0);
     L.hot_bytes = (int)((B.b.size() + 15) & ~size_t(15));
     // cold tables (read once per cell from global memory)

@@ -30,7 +30,6 @@ template <int NP, int NSLOT>
 DFC_HD double load_cell_state(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* regs, int dfc_lane,
                               const double* Y, int ldY, int cell, double T, double p, double& ysum) {
     (void)dfc_lane;
-    double* red = sm + m.off_red;
     double* c = sm + m.off_c;
     double* cs = sm + m.off_cs;
     DFC_LANES_BEGIN
@@ -40,16 +39,16 @@ DFC_HD double load_cell_state(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>*
         c[k] = y;  // raw mass fraction for now
         s += y;
     }
-    red[tl] = s;
+    DFC_LR.red = s;
     DFC_LANES_END
-    ysum = team_sum(red);
+    ysum = team_sum(regs);
     const double rys = 1.0 / ysum;
     DFC_LANES_BEGIN
     double s = 0.0;
     for (int k = tl; k < m.N; k += kTeam) s += c[k] * rys / DFC_LDG(m.W + k);
-    red[tl] = s;
+    DFC_LR.red = s;
     DFC_LANES_END
-    const double wbar = 1.0 / team_sum(red);
+    const double wbar = 1.0 / team_sum(regs);
     const double rho_ct = p * wbar / (kGasConstant * T);
     DFC_LANES_BEGIN
     for (int k = tl; k < m.N; k += kTeam) {
@@ -69,6 +68,22 @@ DFC_HD double load_cell_state(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>*
     return rho_ct;
 }
 
+// constant slots the tables rely on: c[N] = cs[N] = 1 (absent factor), q[R] = dq[n_dq] = 0
+// (row-program padding).  Called after setup_rate_constants, which uses dq as scratch.
+DFC_HD void init_const_slots(const DevMech& m, double* sm, int dfc_lane) {
+    (void)dfc_lane;
+    DFC_LANES_BEGIN
+    if (tl == 0) {
+        sm[m.off_c + m.N] = 1.0;
+        sm[m.off_cs + m.N] = 1.0;
+        sm[m.off_c + m.N + 1] = 0.0;
+        sm[m.off_cs + m.N + 1] = 0.0;
+        sm[m.off_q + m.R] = 0.0;
+        sm[m.off_dq + m.n_dq] = 0.0;
+    }
+    DFC_LANES_END
+}
+
 template <int NP, int NSLOT>
 DFC_HD void solve_one_cell(const DevMech& m, const SolveArgs& a, double* sm, LaneRegs<NP, NSLOT>* regs,
                            int dfc_lane, int cell, StepStats& st) {
@@ -77,13 +92,13 @@ DFC_HD void solve_one_cell(const DevMech& m, const SolveArgs& a, double* sm, Lan
     double ysum;
     const double rho_ct = load_cell_state<NP, NSLOT>(m, sm, regs, dfc_lane, a.Y, a.ldY, cell, T, p, ysum);
     setup_rate_constants(m, sm, T, dfc_lane);
+    init_const_slots(m, sm, dfc_lane);
     st = StepStats{0, 0, kCellOk};
     if (dt > 0.0) st = integrate_cell<NP, NSLOT>(m, sm, regs, dfc_lane, dt, a.rtol, a.atol * rho_ct, a.max_steps);
     // RR and Qdot
     const double rho_of = a.rho[cell];
     const double scale = dt > 0.0 ? rho_of / dt : 0.0;
     const double rys = 1.0 / ysum;
-    double* red = sm + m.off_red;
     DFC_LANES_BEGIN
     double qd = 0.0;
     DFC_UNROLL
@@ -106,9 +121,9 @@ DFC_HD void solve_one_cell(const DevMech& m, const SolveArgs& a, double* sm, Lan
         a.RR[(size_t)ko * a.ldRR + cell] = rr;
         qd = fma(-DFC_LDG(m.hc + k), rr, qd);
     }
-    red[tl] = qd;
+    DFC_LR.red = qd;
     DFC_LANES_END
-    const double qdot = team_sum(red);
+    const double qdot = team_sum(regs);
     DFC_LANES_BEGIN
     if (tl == 0) {
         a.Qdot[cell] = qdot;
@@ -127,7 +142,8 @@ DFC_HD void wdot_one_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* reg
     const double Tc = T[cell];
     load_cell_state<NP, NSLOT>(m, sm, regs, dfc_lane, Y, ldY, cell, Tc, p[cell], ysum);
     setup_rate_constants(m, sm, Tc, dfc_lane);
-    eval_wdot(m, sm, sm + m.off_c, sm + m.off_vec, dfc_lane, false);
+    init_const_slots(m, sm, dfc_lane);
+    eval_wdot<false>(m, sm, sm + m.off_c, sm + m.off_vec, regs, dfc_lane);
     DFC_LANES_BEGIN
     for (int k = tl; k < m.N; k += kTeam)
         wr[(size_t)DFC_LDG(m.perm + k) * ldW + cell] = k < m.NA ? sm[m.off_vec + k] * DFC_LDG(m.W + k) : 0.0;

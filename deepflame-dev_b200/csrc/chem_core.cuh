@@ -36,6 +36,7 @@
 #define DFC_LR (*regs)
 #define DFC_LDG(p) __ldg(p)
 #define DFC_UNROLL _Pragma("unroll")
+#define DFC_NOUNROLL _Pragma("unroll 1")
 #define DFC_NOINLINE __noinline__
 #else
 #define DFC_LANES_BEGIN for (int tl = 0; tl < ::dfchem::kTeam; ++tl) {
@@ -44,6 +45,7 @@
 #define DFC_LR (regs[tl])
 #define DFC_LDG(p) (*(p))
 #define DFC_UNROLL
+#define DFC_NOUNROLL
 #define DFC_NOINLINE
 #endif
 
@@ -95,15 +97,29 @@ DFC_HD double rodas_c(int i, int j) {
     }
 }
 
+// Matrices with 33..36 rows use the bordered layout (integrator.cuh): 32 core rows, one per lane,
+// and NB = NP - 32 border rows handled through the Schur complement.
+constexpr int border_rows(int NP) { return (NP > 32 && NP <= 36) ? NP - 32 : 0; }
+
 template <int NP, int NSLOT>
 struct LaneRegs {
-    double a[NSLOT][NP];      // this lane's rows of (I/(h g) - J)^-1, row-unscaled (see gj_invert)
-    double invd[NSLOT];       // 1/pivot of each row: x_row = invd * sum_j a[row][j] b_j
+    static constexpr int NB = border_rows(NP);
+    static constexpr int NBX = NB ? NB : 1;
+    static constexpr int NCOL = NB ? 32 : NP;
+    static constexpr int NROW = NB ? 1 : NSLOT;
+    double a[NROW][NCOL];     // this lane's rows of (I/(h g) - J)^-1, row-unscaled (see gj_invert)
+    double invd[NROW];        // 1/pivot of each row: x_row = invd * sum_j a[row][j] b_j
+    double g[NBX];            // bordered: this row's entries in the border columns -> A11^-1 A12
+    double v[NBX];            // bordered: column `lane` of the border rows -> -A21 A11^-1
+    double S[NBX * NBX];      // bordered: Schur complement, then its inverse (same on every lane)
+    double redv[NBX];         // bordered: this lane's terms of the border dot products
+    double tmp;
     double k[kStages][NSLOT]; // stage increments
     double c0[NSLOT];         // concentrations at t = 0
     double dc[NSLOT];         // accumulated increment c(t) - c0 (kept separately: RR needs c - c0)
     double f0[NSLOT];         // wdot at the step's base point
     double inc[NSLOT];        // increment of the step being tested
+    double red;               // this lane's term of a team reduction (team_sum)
 };
 
 struct D2 {
@@ -146,119 +162,194 @@ DFC_HD double nasa_s_R(const double* a, double T, double logT) {
 DFC_HD DevMech rebase_hot(const DevMech& m, const uint8_t* nb) {
     DevMech r = m;
     const uint8_t* ob = m.hot_base;
+#define DFC_REBASE(field, T) r.field = reinterpret_cast<const T*>(nb + (reinterpret_cast<const uint8_t*>(m.field) - ob))
     r.hot_base = nb;
-    r.rdesc = reinterpret_cast<const U4*>(nb + (reinterpret_cast<const uint8_t*>(m.rdesc) - ob));
-    r.coef = reinterpret_cast<const double*>(nb + (reinterpret_cast<const uint8_t*>(m.coef) - ob));
-    r.ms_dflt = reinterpret_cast<const double*>(nb + (reinterpret_cast<const uint8_t*>(m.ms_dflt) - ob));
-    r.ms_val = reinterpret_cast<const double*>(nb + (reinterpret_cast<const uint8_t*>(m.ms_val) - ob));
-    r.ms_ptr = reinterpret_cast<const int*>(nb + (reinterpret_cast<const uint8_t*>(m.ms_ptr) - ob));
-    r.ms_idx = reinterpret_cast<const int*>(nb + (reinterpret_cast<const uint8_t*>(m.ms_idx) - ob));
-    r.wdotA.ent = reinterpret_cast<const uint32_t*>(nb + (reinterpret_cast<const uint8_t*>(m.wdotA.ent) - ob));
-    r.wdotB.ent = reinterpret_cast<const uint32_t*>(nb + (reinterpret_cast<const uint8_t*>(m.wdotB.ent) - ob));
-    r.jac.ent = reinterpret_cast<const uint32_t*>(nb + (reinterpret_cast<const uint8_t*>(m.jac.ent) - ob));
+    DFC_REBASE(rdesc, U4);
+    DFC_REBASE(coef, double);
+    DFC_REBASE(msets.ent, U4);
+    DFC_REBASE(msets.dst, uint32_t);
+    DFC_REBASE(wdotA.ent, U4);
+    DFC_REBASE(wdotA.dst, uint32_t);
+    DFC_REBASE(wdotB, uint32_t);
+    DFC_REBASE(jac.ent, U4);
+    DFC_REBASE(jac.dst, uint32_t);
+#undef DFC_REBASE
     return r;
 }
 
-// team-uniform sum of the 32 partials in red[]
-DFC_HD double team_sum(const double* red) {
-    double s = 0.0;
-    DFC_UNROLL
-    for (int i = 0; i < kTeam; i += 2) {
-        D2 v = ld2(red + i);
-        s += v.x;
-        s += v.y;
-    }
+// byte-offset addressing of the per-cell arrays (offsets come pre-scaled from the tables)
+DFC_HD double ldb(const double* base, uint32_t byte_off) {
+    return *reinterpret_cast<const double*>(reinterpret_cast<const char*>(base) + byte_off);
+}
+DFC_HD double* ptrb(double* base, uint32_t byte_off) {
+    return reinterpret_cast<double*>(reinterpret_cast<char*>(base) + byte_off);
+}
+DFC_HD U4 ld_u4(const U4* p) {
 #ifdef __CUDA_ARCH__
-    __syncwarp();  // red[] may be rewritten by the next lane block
+    const uint4 v = *reinterpret_cast<const uint4*>(p);
+    return U4{v.x, v.y, v.z, v.w};
+#else
+    return *p;
 #endif
-    return s;
+}
+// +/- v selected by bit 31 of the entry word (one LOP3 on the high half of the double)
+DFC_HD double signed_by(double v, uint32_t e) {
+#ifdef __CUDA_ARCH__
+    return __hiloint2double(__double2hiint(v) ^ (int)(e & 0x80000000u), __double2loint(v));
+#else
+    return (e & 0x80000000u) ? -v : v;
+#endif
 }
 
-// ---- third-body concentrations M_s for the efficiency sets -----------------------------------
-DFC_HD void compute_msets(const DevMech& m, double* sm, const double* cx, int dfc_lane) {
+// Sum over the team of one value per lane (the lane's value is DFC_LR.red).  Device: xor
+// butterfly through warp shuffles, every lane ends with the same bits.  Host emulation: the same
+// butterfly evaluated for lane 0.
+template <class Regs>
+DFC_HD double team_sum(Regs* regs) {
+#ifdef __CUDA_ARCH__
+    double v = regs->red;
+    DFC_UNROLL
+    for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+#else
+    double t[kTeam];
+    for (int i = 0; i < kTeam; ++i) t[i] = regs[i].red;
+    for (int d = 16; d >= 1; d >>= 1)
+        for (int i = 0; i < d; ++i) t[i] += t[i + d];
+    return t[0];
+#endif
+}
+
+// the same for NB values per lane (DFC_LR.redv[b]) -> z[b]
+template <int NB, class Regs>
+DFC_HD void team_sum_n(Regs* regs, double* z) {
+#ifdef __CUDA_ARCH__
+    DFC_UNROLL
+    for (int b = 0; b < NB; ++b) z[b] = regs->redv[b];
+    DFC_UNROLL
+    for (int d = 16; d >= 1; d >>= 1) {
+        DFC_UNROLL
+        for (int b = 0; b < NB; ++b) z[b] += __shfl_xor_sync(0xffffffffu, z[b], d);
+    }
+#else
+    for (int b = 0; b < NB; ++b) {
+        double t[kTeam];
+        for (int i = 0; i < kTeam; ++i) t[i] = regs[i].redv[b];
+        for (int d = 16; d >= 1; d >>= 1)
+            for (int i = 0; i < d; ++i) t[i] += t[i + d];
+        z[b] = t[0];
+    }
+#endif
+}
+
+// ---- row programs (see RowProg) ---------------------------------------------------------------
+DFC_HD void run_rows(const RowProg& g, const double* coef, const double* src, double* dst, int dfc_lane) {
     (void)dfc_lane;
-    if (m.n_msets == 0) return;
-    double* red = sm + m.off_red;
     DFC_LANES_BEGIN
-    double s = 0.0;
-    for (int k = tl; k < m.N; k += kTeam) s += cx[k];
-    red[tl] = s;
-    DFC_LANES_END
-    const double ctot = team_sum(red);
-    DFC_LANES_BEGIN
-    for (int s = tl; s < m.n_msets; s += kTeam) {
-        double M = m.ms_dflt[s] * ctot;  // hot tables may live in shared memory: plain loads
-        for (int q = m.ms_ptr[s]; q < m.ms_ptr[s + 1]; ++q) M += m.ms_val[q] * cx[m.ms_idx[q]];
-        sm[m.off_M + s] = M;
+    const U4* e = g.ent + tl;
+    const uint32_t* dp = g.dst + tl;
+    DFC_NOUNROLL
+    for (int i = 0; i < g.nA; ++i, e += kTeam, dp += kTeam) {
+        const U4 u = ld_u4(e);
+        const uint32_t d = *dp;
+        const double v0 = signed_by(ldb(src, u.x & 0xFFFFu), u.x);
+        const double v1 = signed_by(ldb(src, u.y & 0xFFFFu), u.y);
+        const double v2 = signed_by(ldb(src, u.z & 0xFFFFu), u.z);
+        const double v3 = signed_by(ldb(src, u.w & 0xFFFFu), u.w);
+        double sum = (v0 + v1) + (v2 + v3);
+        if (d != kRowSkip) {
+            double* out = ptrb(dst, d & 0xFFFFFFu);
+            if (d & kRowAcc) sum += *out;
+            *out = sum;
+        }
+    }
+    DFC_NOUNROLL
+    for (int i = 0; i < g.nB; ++i, e += kTeam, dp += kTeam) {
+        const U4 u = ld_u4(e);
+        const uint32_t d = *dp;
+        double s0 = coef[(u.x >> 16) & 0x7Fu] * ldb(src, u.x & 0xFFFFu);
+        double s1 = coef[(u.y >> 16) & 0x7Fu] * ldb(src, u.y & 0xFFFFu);
+        s0 = fma(coef[(u.z >> 16) & 0x7Fu], ldb(src, u.z & 0xFFFFu), s0);
+        s1 = fma(coef[(u.w >> 16) & 0x7Fu], ldb(src, u.w & 0xFFFFu), s1);
+        double sum = s0 + s1;
+        if (d != kRowSkip) {
+            double* out = ptrb(dst, d & 0xFFFFFFu);
+            if (d & kRowAcc) sum += *out;
+            *out = sum;
+        }
     }
     DFC_LANES_END
+}
+
+// c^o and its derivative with Cantera's rule for non-integer orders (non-positive c -> 0).
+// Rare (global one-step mechanisms): kept out of line so the hot loop stays small.
+#if defined(__CUDACC__)
+__host__ __device__ DFC_NOINLINE
+#else
+inline
+#endif
+D2 pow_factor(double o, double c) {
+    if (o == 1.0) return D2{c, 1.0};
+    if (o == 2.0) return D2{c * c, 2.0 * c};
+    if (o == 3.0) return D2{c * c * c, 3.0 * c * c};
+    if (c > 0.0) return D2{pow(c, o), o * pow(c, o - 1.0)};
+    return D2{0.0, 0.0};
 }
 
 // ---- rates of progress q_r (and, if JAC, the partial derivatives) ----------------------------
 // Lane-per-reaction.  Rate laws: SURVEY Appendix A.2-A.6 (Cantera GasKinetics semantics).
+// cx: [N + 2] concentrations with cx[N] = 1 (absent factor); M_s already evaluated.
 template <bool JAC>
 DFC_HD void eval_reactions(const DevMech& m, double* sm, const double* cx, int dfc_lane) {
     (void)dfc_lane;
-    const double* kf = sm + m.off_kf;
-    const double* rkc = sm + m.off_rkc;
+    const double* kfk = sm + m.off_kf;
     double* q = sm + m.off_q;
     double* dq = sm + m.off_dq;
+    const uint32_t none = (uint32_t)m.N << 3;
     DFC_LANES_BEGIN
     for (int r = tl; r < m.R; r += kTeam) {
-#ifdef __CUDA_ARCH__
-        const uint4 dd = *(reinterpret_cast<const uint4*>(m.rdesc) + r);
-        const U4 d{dd.x, dd.y, dd.z, dd.w};
-#else
-        const U4 d = m.rdesc[r];
-#endif
-        const uint32_t flags = (d.y >> 16) & 0xFFu;
-        const uint32_t kind = flags & 3u;
-        int fi[3] = {(int)(d.x & 0xFF), (int)((d.x >> 8) & 0xFF), (int)((d.x >> 16) & 0xFF)};
-        int pi[3] = {(int)(d.x >> 24), (int)(d.y & 0xFF), (int)((d.y >> 8) & 0xFF)};
+        const U4 d = ld_u4(m.rdesc + r);
+        const uint32_t kind = d.x & 3u;
+        const uint32_t fo[3] = {d.x & 0x7F8u, (d.x >> 8) & 0x7F8u, (d.x >> 16) & 0x7F8u};
+        const uint32_t po[3] = {d.y & 0x7F8u, (d.y >> 8) & 0x7F8u, (d.y >> 16) & 0x7F8u};
         double fv[3], fd[3], pv[3], pd[3];
-        if (!(flags & kFlagPow)) {
+        if (!(d.x & kFlagPow)) {
             DFC_UNROLL
             for (int a = 0; a < 3; ++a) {
-                fv[a] = fi[a] != 255 ? cx[fi[a]] : 1.0;
-                pv[a] = pi[a] != 255 ? cx[pi[a]] : 1.0;
+                fv[a] = ldb(cx, fo[a]);
+                pv[a] = ldb(cx, po[a]);
                 fd[a] = 1.0;
                 pd[a] = 1.0;
             }
         } else {
             // fractional / large orders: c^o with Cantera's rule (non-positive c -> 0)
-            const double* pw = m.powtab + (size_t)(d.z >> 16) * 9;
+            const double* pw = m.powtab + (size_t)(d.z >> 20) * 9;
             for (int a = 0; a < 3; ++a) {
                 fv[a] = pv[a] = 1.0;
                 fd[a] = pd[a] = 0.0;
-                if (fi[a] != 255) {
-                    const double o = DFC_LDG(pw + a), c = cx[fi[a]];
-                    if (o == 1.0) { fv[a] = c; fd[a] = 1.0; }
-                    else if (o == 2.0) { fv[a] = c * c; fd[a] = 2.0 * c; }
-                    else if (o == 3.0) { fv[a] = c * c * c; fd[a] = 3.0 * c * c; }
-                    else if (c > 0.0) { fv[a] = pow(c, o); fd[a] = o * pow(c, o - 1.0); }
-                    else { fv[a] = 0.0; fd[a] = 0.0; }
+                if (fo[a] != none) {
+                    const D2 t = pow_factor(DFC_LDG(pw + a), ldb(cx, fo[a]));
+                    fv[a] = t.x;
+                    fd[a] = t.y;
                 }
-                if (pi[a] != 255) {
-                    const double o = DFC_LDG(pw + 6 + a), c = cx[pi[a]];
-                    if (o == 1.0) { pv[a] = c; pd[a] = 1.0; }
-                    else if (o == 2.0) { pv[a] = c * c; pd[a] = 2.0 * c; }
-                    else if (o == 3.0) { pv[a] = c * c * c; pd[a] = 3.0 * c * c; }
-                    else if (c > 0.0) { pv[a] = pow(c, o); pd[a] = o * pow(c, o - 1.0); }
-                    else { pv[a] = 0.0; pd[a] = 0.0; }
+                if (po[a] != none) {
+                    const D2 t = pow_factor(DFC_LDG(pw + 6 + a), ldb(cx, po[a]));
+                    pv[a] = t.x;
+                    pd[a] = t.y;
                 }
             }
         }
-        double kfe = kf[r];
+        const D2 kk = ld2(kfk + 2 * r);  // kf, 1/Kc
+        double kfe = kk.x;
         double dkdM = 0.0;
         if (kind != (uint32_t)kElementary) {
-            const double M = sm[m.off_M + (d.y >> 24)];
+            const double M = sm[m.off_M + (d.z & 0xFFu)];
             if (kind == (uint32_t)kThreeBody) {
                 dkdM = kfe;
                 kfe *= M;
             } else {
-                const int fid = (int)(d.z & 0xFFFF);
-                const double k0 = sm[m.off_k0 + fid];
-                const double rk = k0 / (kfe + kSmall);
+                const int fid = (int)((d.z >> 8) & 0xFFFu);
+                const double rk = sm[m.off_k0 + fid];  // k0 / kinf
                 const double pr = M * rk;
                 double F = 1.0, dF_dpr = 0.0;
                 if (kind == (uint32_t)kFalloffTroe) {
@@ -268,10 +359,11 @@ DFC_HD void eval_reactions(const DevMech& m, double* sm, const double* cx, int d
                     const double nn = 0.75 - 1.27 * lf;
                     const double x = lpr + cc;
                     const double den = nn - 0.14 * x;
-                    const double f1 = x / den;
+                    const double rden = 1.0 / den;
+                    const double f1 = x * rden;
                     const double g = 1.0 / (1.0 + f1 * f1);
                     F = exp10(lf * g);
-                    if (JAC && pr > kSmall) dF_dpr = F * (-lf * 2.0 * f1 * g * g * (nn / (den * den))) / pr;
+                    if (JAC && pr > kSmall) dF_dpr = F * (-lf * 2.0 * f1 * g * g * (nn * rden * rden)) / pr;
                 }
                 const double ip = 1.0 / (1.0 + pr);
                 if (JAC) dkdM = kfe * (F * ip * ip + pr * ip * dF_dpr) * rk;
@@ -280,74 +372,68 @@ DFC_HD void eval_reactions(const DevMech& m, double* sm, const double* cx, int d
         }
         const double Pf = fv[0] * fv[1] * fv[2];
         const double Pp = pv[0] * pv[1] * pv[2];
-        const double kre = kfe * rkc[r];
+        const double kre = kfe * kk.y;
         q[r] = kfe * Pf - kre * Pp;
         if (JAC) {
             int slot = (int)d.w;
-            if (fi[0] != 255) dq[slot++] = kfe * fd[0] * fv[1] * fv[2];
-            if (fi[1] != 255) dq[slot++] = kfe * fv[0] * fd[1] * fv[2];
-            if (fi[2] != 255) dq[slot++] = kfe * fv[0] * fv[1] * fd[2];
-            if (pi[0] != 255) dq[slot++] = -kre * pd[0] * pv[1] * pv[2];
-            if (pi[1] != 255) dq[slot++] = -kre * pv[0] * pd[1] * pv[2];
-            if (pi[2] != 255) dq[slot++] = -kre * pv[0] * pv[1] * pd[2];
-            if (kind != (uint32_t)kElementary) dq[slot] = dkdM * (Pf - rkc[r] * Pp);
+            if (fo[0] != none) dq[slot++] = kfe * fd[0] * fv[1] * fv[2];
+            if (fo[1] != none) dq[slot++] = kfe * fv[0] * fd[1] * fv[2];
+            if (fo[2] != none) dq[slot++] = kfe * fv[0] * fv[1] * fd[2];
+            if (po[0] != none) dq[slot++] = -kre * pd[0] * pv[1] * pv[2];
+            if (po[1] != none) dq[slot++] = -kre * pv[0] * pd[1] * pv[2];
+            if (po[2] != none) dq[slot++] = -kre * pv[0] * pv[1] * pd[2];
+            if (kind != (uint32_t)kElementary) dq[slot] = dkdM * (Pf - kk.y * Pp);
         }
     }
     DFC_LANES_END
 }
 
-// ---- segmented gather (see GatherProg) --------------------------------------------------------
-DFC_HD void run_gather(const GatherProg& g, const double* coef, const double* src, double* dst,
-                       int dfc_lane) {
+// wdot_i (i < NA) at concentrations cx -> out[i].  cx is one of the cell's c / cs arrays
+// ([N + 2]: slot N = 1.0, slot N+1 receives the total concentration).
+template <bool JAC, class Regs>
+DFC_HD void eval_wdot(const DevMech& m, double* sm, double* cx, double* out, Regs* regs, int dfc_lane) {
     (void)dfc_lane;
+    if (m.n_msets > 0) {
+        DFC_LANES_BEGIN
+        double s = 0.0;
+        for (int k = tl; k < m.N; k += kTeam) s += cx[k];
+        DFC_LR.red = s;
+        DFC_LANES_END_NOSYNC
+        const double ctot = team_sum(regs);
+        DFC_LANES_BEGIN
+        if (tl == 0) cx[m.N + 1] = ctot;
+        DFC_LANES_END
+        run_rows(m.msets, m.coef, cx, sm + m.off_M, dfc_lane);
+    }
+    if (JAC) {
+        // the dq scratch is shared with part / vec / row (dead by now): restore its zero slot
+        DFC_LANES_BEGIN
+        if (tl == 0) sm[m.off_dq + m.n_dq] = 0.0;
+        DFC_LANES_END_NOSYNC
+    }
+    eval_reactions<JAC>(m, sm, cx, dfc_lane);
+    // J = d wdot / d c from the reaction derivatives; must run before part/out overwrite dq
+    if (JAC) run_rows(m.jac, m.coef, sm + m.off_dq, sm + m.off_J, dfc_lane);
+    run_rows(m.wdotA, m.coef, sm + m.off_q, sm + m.off_part, dfc_lane);
+    const double* part = sm + m.off_part;
     DFC_LANES_BEGIN
-    double acc = 0.0;
-    const uint32_t* e = g.ent + tl * 4;
-    for (int it = 0; it < g.n_iter; it += 4, e += 4 * kTeam) {
-        // four entries per 16-byte load; all loads of the batch are issued before the FMA chain
-#ifdef __CUDA_ARCH__
-        const uint4 uu = *reinterpret_cast<const uint4*>(e);
-        const uint32_t u[4] = {uu.x, uu.y, uu.z, uu.w};
-#else
-        const uint32_t u[4] = {e[0], e[1], e[2], e[3]};
-#endif
-        double cf[4], sv[4];
-        DFC_UNROLL
-        for (int b = 0; b < 4; ++b) {
-            cf[b] = coef[(u[b] >> 12) & 0x7Fu];
-            sv[b] = src[u[b] & 0xFFFu];
+    for (int i = tl; i < m.NA; i += kTeam) {
+        const uint32_t w = m.wdotB[i];
+        const double* p = part + (w & 0xFFFFu);
+        const int n = (int)(w >> 16);
+        double s0 = 0.0, s1 = 0.0;
+        int j = 0;
+        for (; j + 1 < n; j += 2) {
+            s0 += p[j];
+            s1 += p[j + 1];
         }
-        DFC_UNROLL
-        for (int b = 0; b < 4; ++b) {
-            acc = fma(cf[b], sv[b], acc);
-            if (u[b] & (1u << 19)) {
-                dst[u[b] >> 20] = acc;
-                acc = 0.0;
-            }
-        }
+        if (j < n) s0 += p[j];
+        out[i] = s0 + s1;
     }
     DFC_LANES_END
 }
 
-// wdot_i (i < NA) at concentrations cx -> out[i].  Deliberately NOT inlined on the device: it is
-// called from seven sites per Rosenbrock step and the kernel must stay instruction-cache resident.
-#if defined(__CUDACC__)
-__host__ __device__ DFC_NOINLINE
-#else
-inline
-#endif
-void eval_wdot(const DevMech& m, double* sm, const double* cx, double* out, int dfc_lane,
-                      bool jac) {
-    compute_msets(m, sm, cx, dfc_lane);
-    if (jac)
-        eval_reactions<true>(m, sm, cx, dfc_lane);
-    else
-        eval_reactions<false>(m, sm, cx, dfc_lane);
-    run_gather(m.wdotA, m.coef, sm + m.off_q, sm + m.off_part, dfc_lane);
-    run_gather(m.wdotB, m.coef, sm + m.off_part, out, dfc_lane);
-}
-
-// ---- per-cell constants of the frozen-T sub-step: kf, 1/Kc, falloff k0 and log10 Fcent --------
+// ---- per-cell constants of the frozen-T sub-step: kf, 1/Kc, falloff k0/kinf and log10 Fcent ---
 DFC_HD void setup_rate_constants(const DevMech& m, double* sm, double T, int dfc_lane) {
     (void)dfc_lane;
     const double logT = log(T), rT = 1.0 / T;
@@ -357,39 +443,39 @@ DFC_HD void setup_rate_constants(const DevMech& m, double* sm, double T, int dfc
         const double* a = nasa_sel(m, k, T);
         g[k] = nasa_h_RT(a, T) - nasa_s_R(a, T, logT);
     }
-    if (tl == 0) sm[m.off_part] = 0.0;
     DFC_LANES_END
     const double log_c0 = log(kOneAtm / (kGasConstant * T));
+    const uint32_t none = (uint32_t)m.N << 3;
     DFC_LANES_BEGIN
     for (int r = tl; r < m.R; r += kTeam) {
         const U4 d = m.rdesc[r];
-        const uint32_t flags = (d.y >> 16) & 0xFFu;
         const double* ar = m.arrh + (size_t)r * 3;
-        sm[m.off_kf + r] = exp(DFC_LDG(ar) + DFC_LDG(ar + 1) * logT - DFC_LDG(ar + 2) * rT);
+        const double lnk = DFC_LDG(ar) + DFC_LDG(ar + 1) * logT - DFC_LDG(ar + 2) * rT;
         double rk = 0.0;
-        if (flags & kFlagRev) {
-            int fi[3] = {(int)(d.x & 0xFF), (int)((d.x >> 8) & 0xFF), (int)((d.x >> 16) & 0xFF)};
-            int pi[3] = {(int)(d.x >> 24), (int)(d.y & 0xFF), (int)((d.y >> 8) & 0xFF)};
+        if (d.x & kFlagRev) {
+            const uint32_t fo[3] = {d.x & 0x7F8u, (d.x >> 8) & 0x7F8u, (d.x >> 16) & 0x7F8u};
+            const uint32_t po[3] = {d.y & 0x7F8u, (d.y >> 8) & 0x7F8u, (d.y >> 16) & 0x7F8u};
             double dG = 0.0, dn = 0.0;
-            if (!(flags & kFlagPow)) {
+            if (!(d.x & kFlagPow)) {
                 for (int a = 0; a < 3; ++a) {
-                    if (fi[a] != 255) { dG -= g[fi[a]]; dn -= 1.0; }
-                    if (pi[a] != 255) { dG += g[pi[a]]; dn += 1.0; }
+                    if (fo[a] != none) { dG -= ldb(g, fo[a]); dn -= 1.0; }
+                    if (po[a] != none) { dG += ldb(g, po[a]); dn += 1.0; }
                 }
             } else {
-                const double* pw = m.powtab + (size_t)(d.z >> 16) * 9;
+                const double* pw = m.powtab + (size_t)(d.z >> 20) * 9;
                 for (int a = 0; a < 3; ++a) {
-                    if (fi[a] != 255) { dG -= pw[3 + a] * g[fi[a]]; dn -= pw[3 + a]; }
-                    if (pi[a] != 255) { dG += pw[6 + a] * g[pi[a]]; dn += pw[6 + a]; }
+                    if (fo[a] != none) { dG -= pw[3 + a] * ldb(g, fo[a]); dn -= pw[3 + a]; }
+                    if (po[a] != none) { dG += pw[6 + a] * ldb(g, po[a]); dn += pw[6 + a]; }
                 }
             }
             rk = fmin(exp(dG - dn * log_c0), kBig);
         }
-        sm[m.off_rkc + r] = rk;
-        if ((flags & 3u) >= (uint32_t)kFalloffLindemann) {
-            const int fid = (int)(d.z & 0xFFFF);
+        st2(sm + m.off_kf + 2 * r, exp(lnk), rk);
+        if ((d.x & 3u) >= (uint32_t)kFalloffLindemann) {
+            const int fid = (int)((d.z >> 8) & 0xFFFu);
             const double* f = m.fall + (size_t)fid * 8;
-            sm[m.off_k0 + fid] = exp(f[0] + f[1] * logT - f[2] * rT);
+            // k0 / kinf as one exponential (kinf = 0 cannot occur: ln A is finite for falloff)
+            sm[m.off_k0 + fid] = fmin(exp(f[0] + f[1] * logT - f[2] * rT - lnk), 1e200);
             double lf = 0.0;
             if (f[7] != 0.0) {
                 double fc = (1.0 - f[3]) * exp(-T / f[4]) + f[3] * exp(-T / f[5]);

@@ -24,35 +24,46 @@ struct alignas(16) U4 {
     uint32_t x, y, z, w;
 };
 
-// Lane-blocked "segmented gather" program.  Lane l executes, for it = 0..n_iter-1, the entry
-// ent[(it/4)*4*kTeam + l*4 + it%4] (four consecutive entries of a lane are one 16-byte load):
-//   acc += coef[e.coef] * src[e.src];  if (e.store) { dst[e.dst] = acc; acc = 0; }
-// Every destination is written by exactly one lane, so no atomics are needed.  n_iter % 4 == 0.
-//   bits 0-11 src | bits 12-18 coef id | bit 19 store | bits 20-31 dst
-struct GatherProg {
-    int n_iter;
-    const uint32_t* ent;
+// Lane-blocked "row program": a sparse matrix-vector product scheduled at mechanism-compile time.
+// Lane l executes rows i = 0..n_rows-1; row i of lane l is the 16-byte record ent[i*kTeam + l]
+// (four entries, one LDS.128) plus the word dst[i*kTeam + l].  The row sums its four entries and
+// stores (or, with the accumulate flag, adds) the sum to *(double*)(dst_base + (dst & 0xFFFFFF)).
+//   type-A rows (i < nA): value = +/- src            entry = src_byte_offset | sign << 31
+//   type-B rows (i >= nA): value = coef[id] * src    entry = src_byte_offset | id << 16
+// Integer stoichiometric coefficients are expanded into repeated +/-1 entries, so the common case
+// needs no coefficient load and no multiply.  Padding entries point at a slot that holds 0.0
+// (type A) or use coef[0] = 0 (type B).  dst == kRowSkip marks a padding row.  Rows that share a
+// destination are scheduled on the same lane in program order, so `accumulate` needs no atomics.
+constexpr uint32_t kRowSkip = 0xFFFFFFFFu, kRowAcc = 0x80000000u;
+struct RowProg {
+    int nA, nB;
+    const U4* ent;
+    const uint32_t* dst;
 };
 
 // Reaction descriptor (16 B).  A side holds up to 3 concentration factors; an integer
 // stoichiometric coefficient/order nu is expanded into nu repeated factors ("2 OH" -> OH, OH),
-// so products and the product rule for derivatives need no exponent.  Reactions that do not fit
+// so products and the product rule for derivatives need no exponent.  An absent factor is the
+// index N: slot N of the concentration array always holds 1.0.  Reactions that do not fit
 // (fractional `orders`, more than 3 molecules on a side) use the pow path: factors are the
 // distinct species and powtab[pow_id*9 + {0..2 order, 3..5 reactant nu, 6..8 product nu}].
-//   x = rf0 | rf1<<8 | rf2<<16 | pf0<<24          (0xFF = empty)
-//   y = pf1 | pf2<<8 | flags<<16 | mset<<24        flags: bits0-1 kind, bit2 reversible, bit3 pow
-//   z = fall_id | pow_id<<16
+// Factor fields are stored pre-scaled (index*8 = byte offset of the double):
+//   x = kind | rev<<2 | rf0<<3 | rf1<<11 | rf2<<19 | pow<<27
+//   y =                 pf0<<3 | pf1<<11 | pf2<<19
+//   z = mset | fall_id<<8 | pow_id<<20
 //   w = dq_off   first slot of this reaction in the per-cell derivative scratch; slot order:
 //                present reactant factors, present product factors (reversible only),
 //                d q/d[M] (three-body / falloff only)
-constexpr uint32_t kFlagRev = 4u, kFlagPow = 8u;
+constexpr uint32_t kFlagRev = 4u, kFlagPow = 1u << 27;
 
 struct DevMech {
     int N, NA, NP, R, n_msets, n_fall, n_pow, n_dq, n_part, ldj;  // NP: padded NA (kernel template)
     // per-cell shared-memory layout, offsets in doubles from the cell's base (all even)
-    int off_c, off_cs, off_kf, off_rkc, off_k0, off_lfc, off_M, off_q, off_dq, off_J, off_vec,
+    // c, cs: [N + 2] concentrations, slot N = 1.0 (absent factor), slot N+1 = sum of all N
+    // kf: [2R] interleaved (kf_r, 1/Kc_r);  q: [R + 1], slot R = 0.0;  dq: [n_dq + 1], last = 0.0
+    int off_c, off_cs, off_kf, off_k0, off_lfc, off_M, off_q, off_dq, off_J, off_vec,
         off_row, off_part, off_red, cell_doubles;
-    // hot tables (rdesc, coef, efficiency sets, gather programs) are one contiguous prefix of the
+    // hot tables (rdesc, coef, row programs) are one contiguous prefix of the
     // table blob; the kernels stage it in shared memory once per CTA (rebase_hot)
     const uint8_t* hot_base;
     int hot_bytes;
@@ -68,15 +79,12 @@ struct DevMech {
     const double* fall;    // [n_fall*8] ln A0, b0, Ea0/R, Troe A, T3, T1, T2, is_troe
     const double* powtab;  // [n_pow*9]
     // third-body efficiency sets: M_s = dflt_s*Ctot + sum_j (eff_sj - dflt_s) c_j
-    const double* ms_dflt; // [n_msets]
-    const int* ms_ptr;     // [n_msets+1]
-    const int* ms_idx;     // species (internal)
-    const double* ms_val;  // eff - dflt
-    // gather programs
+    // row programs
     const double* coef;    // distinct coefficients, coef[0] = 0
-    GatherProg wdotA;      // q[R] -> part[n_part]
-    GatherProg wdotB;      // part -> w[NA]
-    GatherProg jac;        // dq[n_dq] -> J[(NA+1)*ldj]; column NA holds gsum_i = sum_r nu_ir dflt_r dq_r/d[M]
+    RowProg msets;         // c[N+2] -> M[n_msets]
+    RowProg wdotA;         // q[R+1] -> part[n_part]  (each species' partial sums are contiguous)
+    const uint32_t* wdotB; // [NP] first partial | count << 16 : w_i = sum of its partials
+    RowProg jac;           // dq[n_dq+1] -> J[(NA+1)*ldj]; column NA holds gsum_i = sum_r nu_ir dflt_r dq_r/d[M]
 };
 
 // Host-side owner of the table storage.  `blob` is one contiguous byte array; DevMech pointers

@@ -7,7 +7,10 @@
         case 20: CALL(20, 1); break;                                     \
         case 24: CALL(24, 1); break;                                     \
         case 32: CALL(32, 1); break;                                     \
+        case 33: CALL(33, 2); break;                                     \
         case 34: CALL(34, 2); break;                                     \
+        case 35: CALL(35, 2); break;                                     \
+        case 36: CALL(36, 2); break;                                     \
         case 40: CALL(40, 2); break;                                     \
         case 48: CALL(48, 2); break;                                     \
         case 64: CALL(64, 2); break;                                     \

@@ -122,8 +122,234 @@ struct StepStats {
     int accepted, rejected, status;
 };
 
+// RODAS4 stage combinations with the stage index as a run-time value (the stage loop is a real
+// loop so that eval_wdot is instantiated once); the stage increments stay in registers because
+// every access below uses a compile-time index.
+template <int NSLOT>
+DFC_HD double stage_point(int i, const double (&k)[kStages][NSLOT], int s, double v) {
+    switch (i) {
+        case 1: v = fma(rodas_a(1, 0), k[0][s], v); break;
+        case 2: v = fma(rodas_a(2, 0), k[0][s], v); v = fma(rodas_a(2, 1), k[1][s], v); break;
+        case 3:
+            v = fma(rodas_a(3, 0), k[0][s], v); v = fma(rodas_a(3, 1), k[1][s], v);
+            v = fma(rodas_a(3, 2), k[2][s], v);
+            break;
+        default:  // stages 4 and 5 share a_4j; stage 5 adds k_4
+            v = fma(rodas_a(4, 0), k[0][s], v); v = fma(rodas_a(4, 1), k[1][s], v);
+            v = fma(rodas_a(4, 2), k[2][s], v); v = fma(rodas_a(4, 3), k[3][s], v);
+            if (i == 5) v += k[4][s];
+            break;
+    }
+    return v;
+}
+template <int NSLOT>
+DFC_HD double stage_rhs(int i, const double (&k)[kStages][NSLOT], int s, double v, double ih) {
+    switch (i) {
+        case 0: break;
+        case 1: v = fma(rodas_c(1, 0) * ih, k[0][s], v); break;
+        case 2: v = fma(rodas_c(2, 0) * ih, k[0][s], v); v = fma(rodas_c(2, 1) * ih, k[1][s], v); break;
+        case 3:
+            v = fma(rodas_c(3, 0) * ih, k[0][s], v); v = fma(rodas_c(3, 1) * ih, k[1][s], v);
+            v = fma(rodas_c(3, 2) * ih, k[2][s], v);
+            break;
+        case 4:
+            v = fma(rodas_c(4, 0) * ih, k[0][s], v); v = fma(rodas_c(4, 1) * ih, k[1][s], v);
+            v = fma(rodas_c(4, 2) * ih, k[2][s], v); v = fma(rodas_c(4, 3) * ih, k[3][s], v);
+            break;
+        default:
+            v = fma(rodas_c(5, 0) * ih, k[0][s], v); v = fma(rodas_c(5, 1) * ih, k[1][s], v);
+            v = fma(rodas_c(5, 2) * ih, k[2][s], v); v = fma(rodas_c(5, 3) * ih, k[3][s], v);
+            v = fma(rodas_c(5, 4) * ih, k[4][s], v);
+            break;
+    }
+    return v;
+}
+template <int NSLOT>
+DFC_HD void stage_store(int i, double (&k)[kStages][NSLOT], int s, double x) {
+    switch (i) {
+        case 0: k[0][s] = x; break;
+        case 1: k[1][s] = x; break;
+        case 2: k[2][s] = x; break;
+        case 3: k[3][s] = x; break;
+        case 4: k[4][s] = x; break;
+        default: k[5][s] = x; break;
+    }
+}
+
+// ---- bordered variant for 33..36 rows ----------------------------------------------------------
+// A = [A11 A12; A21 A22] with A11 the 32 x 32 core (row l on lane l, NSLOT would otherwise double
+// every lane's work for two to four extra rows).  The 32 Gauss-Jordan steps run on the core rows
+// augmented by the border columns (g -> A11^-1 A12, same row scaling as the core), and update
+// the border rows, stored by column (lane j holds column j: v -> -A21 A11^-1) plus the Schur
+// complement S = A22 - A21 A11^-1 A12, which every lane carries redundantly and finally inverts.
+//   x2 = S^-1 (r2 + V r1),   x1 = A11^-1 r1 - (A11^-1 A12) x2          (solve_stage)
+template <int NB>
+DFC_HD void small_inverse(double* S) {
+    DFC_UNROLL
+    for (int k = 0; k < NB; ++k) {
+        const double p = 1.0 / S[k * NB + k];
+        DFC_UNROLL
+        for (int j = 0; j < NB; ++j)
+            if (j != k) S[k * NB + j] *= p;
+        S[k * NB + k] = p;
+        DFC_UNROLL
+        for (int i = 0; i < NB; ++i) {
+            if (i == k) continue;
+            const double f = S[i * NB + k];
+            DFC_UNROLL
+            for (int j = 0; j < NB; ++j)
+                if (j != k) S[i * NB + j] = fma(-f, S[k * NB + j], S[i * NB + j]);
+            S[i * NB + k] = -f * p;
+        }
+    }
+}
+
+template <int NP, int NSLOT>
+DFC_HD void gjb_invert(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* regs, int dfc_lane, double inv_hg) {
+    (void)dfc_lane;
+    constexpr int NB = LaneRegs<NP, NSLOT>::NB;
+    constexpr int RB = (kTeam + 2 * NB + 1) & ~1;  // published pivot record: 32 core + NB aug + NB border
+    const double* J = sm + m.off_J;
+    const int NA = m.NA, ldj = m.ldj;  // NA == NP == 32 + NB
+    DFC_LANES_BEGIN
+    {
+        const double gs = J[NA * ldj + tl];
+        DFC_UNROLL
+        for (int j = 0; j < kTeam; ++j) DFC_LR.a[0][j] = (j == tl ? inv_hg : 0.0) - J[j * ldj + tl] - gs;
+        DFC_UNROLL
+        for (int b = 0; b < NB; ++b) {
+            DFC_LR.g[b] = -J[(kTeam + b) * ldj + tl] - gs;
+            const double gsb = J[NA * ldj + kTeam + b];
+            DFC_LR.v[b] = -J[tl * ldj + kTeam + b] - gsb;
+            DFC_UNROLL
+            for (int b2 = 0; b2 < NB; ++b2)
+                DFC_LR.S[b * NB + b2] = (b == b2 ? inv_hg : 0.0) - J[(kTeam + b2) * ldj + kTeam + b] - gsb;
+        }
+        DFC_LR.invd[0] = 0.0;
+    }
+    DFC_LANES_END
+#ifdef __CUDA_ARCH__
+#pragma unroll 1
+#endif
+    for (int k = 0; k < kTeam; ++k) {
+        double* rowb = sm + m.off_row + (k & 1) * RB;
+        DFC_LANES_BEGIN
+        if (tl == k) {
+            DFC_UNROLL
+            for (int j = 0; j < kTeam; j += 2) st2(rowb + j, DFC_LR.a[0][j], DFC_LR.a[0][j + 1]);
+            DFC_UNROLL
+            for (int b = 0; b < NB; ++b) {
+                rowb[kTeam + b] = DFC_LR.g[b];
+                rowb[kTeam + NB + b] = DFC_LR.v[b];
+            }
+        }
+        DFC_LANES_END
+        DFC_LANES_BEGIN
+        const bool own = tl == k;
+        const double p = 1.0 / rowb[0];
+        const double f = own ? 0.0 : DFC_LR.a[0][0] * p;
+        if (own) DFC_LR.invd[0] = p;
+        const double ur = rowb[(tl - k) & (kTeam - 1)];  // pivot row's entry in logical column `lane`
+        DFC_UNROLL
+        for (int j = 0; j < kTeam; j += 2) {
+            const D2 u = ld2(rowb + j);
+            if (j > 0) DFC_LR.a[0][j - 1] = fma(-f, u.x, DFC_LR.a[0][j]);
+            DFC_LR.a[0][j] = fma(-f, u.y, DFC_LR.a[0][j + 1]);
+        }
+        DFC_LR.a[0][kTeam - 1] = own ? 1.0 : -f;
+        double ug[NB];
+        DFC_UNROLL
+        for (int b = 0; b < NB; ++b) {
+            ug[b] = rowb[kTeam + b];
+            DFC_LR.g[b] = fma(-f, ug[b], DFC_LR.g[b]);
+        }
+        DFC_UNROLL
+        for (int b = 0; b < NB; ++b) {
+            const double fb = rowb[kTeam + NB + b] * p;
+            DFC_LR.v[b] = own ? -fb : fma(-fb, ur, DFC_LR.v[b]);
+            DFC_UNROLL
+            for (int b2 = 0; b2 < NB; ++b2) DFC_LR.S[b * NB + b2] = fma(-fb, ug[b2], DFC_LR.S[b * NB + b2]);
+        }
+        DFC_LANES_END_NOSYNC
+    }
+    DFC_LANES_BEGIN
+    small_inverse<NB>(DFC_LR.S);
+    DFC_LANES_END
+}
+
+// k_i = A^-1 vec for stage i (team level: the bordered variant needs a team reduction)
+template <int NP, int NSLOT>
+DFC_HD void solve_stage(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* regs, int dfc_lane,
+                        const double* vec, int i) {
+    (void)dfc_lane; (void)m; (void)sm;
+    constexpr int NB = LaneRegs<NP, NSLOT>::NB;
+    if constexpr (NB == 0) {
+        DFC_LANES_BEGIN
+        double x[NSLOT];
+        gj_apply<NP, NSLOT>(DFC_LR, vec, x);
+        DFC_UNROLL
+        for (int s = 0; s < NSLOT; ++s) stage_store<NSLOT>(i, DFC_LR.k, s, x[s]);
+        DFC_LANES_END
+    } else {
+        DFC_LANES_BEGIN
+        double acc0 = 0.0, acc1 = 0.0;
+        DFC_UNROLL
+        for (int j = 0; j < kTeam; j += 2) {
+            const D2 b = ld2(vec + j);
+            acc0 = fma(DFC_LR.a[0][j], b.x, acc0);
+            acc1 = fma(DFC_LR.a[0][j + 1], b.y, acc1);
+        }
+        DFC_LR.tmp = acc0 + acc1;
+        const double r1 = vec[tl];
+        DFC_UNROLL
+        for (int b = 0; b < NB; ++b) DFC_LR.redv[b] = DFC_LR.v[b] * r1;
+        DFC_LANES_END_NOSYNC
+        double z[NB];
+        team_sum_n<NB>(regs, z);
+        DFC_LANES_BEGIN
+        double x2[NB];
+        DFC_UNROLL
+        for (int b = 0; b < NB; ++b) {
+            double sacc = 0.0;
+            DFC_UNROLL
+            for (int b2 = 0; b2 < NB; ++b2) sacc = fma(DFC_LR.S[b * NB + b2], vec[kTeam + b2] + z[b2], sacc);
+            x2[b] = sacc;
+        }
+        double x0 = DFC_LR.tmp, x1 = 0.0;
+        DFC_UNROLL
+        for (int b = 0; b < NB; ++b) {
+            x0 = fma(-DFC_LR.g[b], x2[b], x0);
+            if (tl == b) x1 = x2[b];
+        }
+        stage_store<NSLOT>(i, DFC_LR.k, 0, x0 * DFC_LR.invd[0]);
+        stage_store<NSLOT>(i, DFC_LR.k, 1, x1);
+        DFC_LANES_END
+    }
+}
+
+template <int NP, int NSLOT>
+DFC_HD void invert_matrix(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* regs, int dfc_lane, double inv_hg) {
+    if constexpr (LaneRegs<NP, NSLOT>::NB == 0)
+        gj_invert<NP, NSLOT>(m, sm, regs, dfc_lane, inv_hg);
+    else
+        gjb_invert<NP, NSLOT>(m, sm, regs, dfc_lane, inv_hg);
+}
+
+// step-size controller constants (Hairer & Wanner RODAS defaults, wider shrink range after a
+// rejection so that a cold start from h = dt needs few attempts)
+#ifndef DFC_FACMINREJ
+#define DFC_FACMINREJ 0.1
+#endif
+#ifndef DFC_FACMAX
+#define DFC_FACMAX 6.0
+#endif
+#ifndef DFC_FACSAFE
+#define DFC_FACSAFE 0.9
+#endif
+constexpr double kFacSafe = DFC_FACSAFE, kFacMax = DFC_FACMAX, kFacMin = 0.2, kFacMinReject = DFC_FACMINREJ;
+
 // Integrate d c/dt = wdot(c) over [0, dt] for the cell whose state is set up in `sm`
-// (c, cs(inert), kf, rkc, k0, lfc) and regs (c0, dc = 0).  Error control restates the
+// (c, cs(inert), kf, k0, lfc) and regs (c0, dc = 0).  Error control restates the
 // rtol*|Y_k| + atol weights of ReactorNet::setTolerances (dfChemistryModel.C:414) in
 // concentration units: sc_k = atol*rho/W_k + rtol*max(|c_k|, |c_k,new|); WRMS norm over the N
 // species (CVODE's norm also counts the reactor's three constant unknowns).
@@ -135,24 +361,22 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
     double* c = sm + m.off_c;
     double* cs = sm + m.off_cs;
     double* vec = sm + m.off_vec;
-    double* red = sm + m.off_red;
     const int NA = m.NA;
     double t = 0.0, h = dt;
     bool after_reject = false;
-    // zero the padded tail of vec once
-    DFC_LANES_BEGIN
-    for (int j = NA + tl; j < NP; j += kTeam) vec[j] = 0.0;
-    DFC_LANES_END
     while (true) {
-        // base point: f0 = wdot(c), J = d wdot/d c
-        eval_wdot(m, sm, c, vec, dfc_lane, true);
-        run_gather(m.jac, m.coef, sm + m.off_dq, sm + m.off_J, dfc_lane);
+        // base point: f0 = wdot(c), J = d wdot/d c (eval_wdot<true> also runs the Jacobian rows)
+        eval_wdot<true>(m, sm, c, vec, regs, dfc_lane);
         DFC_LANES_BEGIN
         DFC_UNROLL
         for (int s = 0; s < NSLOT; ++s) {
             const int row = tl + kTeam * s;
             DFC_LR.f0[s] = row < NA ? vec[row] : 0.0;
         }
+        DFC_LANES_END
+        // vec shares storage with the derivative scratch: re-zero its padded tail
+        DFC_LANES_BEGIN
+        for (int j = NA + tl; j < NP; j += kTeam) vec[j] = 0.0;
         DFC_LANES_END
         bool accepted = false;
         double hs = 0.0;
@@ -167,44 +391,29 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
                 return st;
             }
             const double ih = 1.0 / hs;
-            gj_invert<NP, NSLOT>(m, sm, regs, dfc_lane, ih / kGamma);
-            DFC_UNROLL
+            invert_matrix<NP, NSLOT>(m, sm, regs, dfc_lane, ih / kGamma);
+#ifdef __CUDA_ARCH__
+#pragma unroll 1
+#endif
             for (int i = 0; i < kStages; ++i) {
                 if (i > 0) {
                     DFC_LANES_BEGIN
                     DFC_UNROLL
                     for (int s = 0; s < NSLOT; ++s) {
                         const int row = tl + kTeam * s;
-                        if (row < NA) {
-                            double v = c[row];
-                            DFC_UNROLL
-                            for (int j = 0; j < i; ++j)
-                                if (rodas_a(i, j) != 0.0) v = fma(rodas_a(i, j), DFC_LR.k[j][s], v);
-                            cs[row] = v;
-                        }
+                        if (row < NA) cs[row] = stage_point<NSLOT>(i, DFC_LR.k, s, c[row]);
                     }
                     DFC_LANES_END
-                    eval_wdot(m, sm, cs, vec, dfc_lane, false);
+                    eval_wdot<false>(m, sm, cs, vec, regs, dfc_lane);
                 }
                 DFC_LANES_BEGIN
                 DFC_UNROLL
                 for (int s = 0; s < NSLOT; ++s) {
                     const int row = tl + kTeam * s;
-                    if (row < NA) {
-                        double v = (i == 0) ? DFC_LR.f0[s] : vec[row];
-                        DFC_UNROLL
-                        for (int j = 0; j < i; ++j)
-                            if (rodas_c(i, j) != 0.0) v = fma(rodas_c(i, j) * ih, DFC_LR.k[j][s], v);
-                        vec[row] = v;
-                    }
+                    if (row < NA) vec[row] = stage_rhs<NSLOT>(i, DFC_LR.k, s, (i == 0) ? DFC_LR.f0[s] : vec[row], ih);
                 }
                 DFC_LANES_END
-                DFC_LANES_BEGIN
-                double x[NSLOT];
-                gj_apply<NP, NSLOT>(DFC_LR, vec, x);
-                DFC_UNROLL
-                for (int s = 0; s < NSLOT; ++s) DFC_LR.k[i][s] = x[s];
-                DFC_LANES_END
+                solve_stage<NP, NSLOT>(m, sm, regs, dfc_lane, vec, i);
             }
             // new solution = argument of the last stage + k_6; error estimate = k_6
             DFC_LANES_BEGIN
@@ -213,9 +422,7 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
             for (int s = 0; s < NSLOT; ++s) {
                 const int row = tl + kTeam * s;
                 if (row < NA) {
-                    double inc = DFC_LR.k[kStages - 1][s];
-                    DFC_UNROLL
-                    for (int j = 0; j < kStages - 1; ++j) inc = fma(rodas_a(kStages - 1, j), DFC_LR.k[j][s], inc);
+                    const double inc = stage_point<NSLOT>(5, DFC_LR.k, s, DFC_LR.k[kStages - 1][s]);
                     DFC_LR.inc[s] = inc;
                     const double cn = c[row] + inc;
                     const double sc = atol_rho / DFC_LDG(m.W + row) + rtol * fmax(fabs(c[row]), fabs(cn));
@@ -223,13 +430,13 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
                     e2 = fma(e, e, e2);
                 }
             }
-            red[tl] = e2;
-            DFC_LANES_END
-            double en = sqrt(team_sum(red) / (double)m.N);
+            DFC_LR.red = e2;
+            DFC_LANES_END_NOSYNC
+            double en = sqrt(team_sum(regs) / (double)m.N);
             if (!(en < 1e30)) en = 1e30;  // NaN / inf -> strong rejection
-            double fac = 0.9 / sqrt(sqrt(fmax(en, 1e-12)));
-            fac = fmin(fmax(fac, 0.2), after_reject ? 1.0 : 6.0);
+            double fac = kFacSafe / sqrt(sqrt(fmax(en, 1e-12)));
             if (en <= 1.0) {
+                fac = fmin(fmax(fac, kFacMin), after_reject ? 1.0 : kFacMax);
                 accepted = true;
                 after_reject = false;
                 ++st.accepted;
@@ -245,6 +452,7 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
                 }
                 DFC_LANES_END
             } else {
+                fac = fmin(fmax(fac, kFacMinReject), 1.0);
                 ++st.rejected;
                 after_reject = true;
             }

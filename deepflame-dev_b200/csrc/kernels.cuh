@@ -26,8 +26,13 @@ solve_kernel(const DevMech mg, const SolveArgs a, unsigned int* queue, unsigned 
     extern __shared__ double2 dfc_smem[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(dfc_smem);
     const DevMech m = stage_hot_tables(mg, smem);
-    const int lane = threadIdx.x % kTeam, warp = threadIdx.x / kTeam;
+    int lane = threadIdx.x % kTeam;
+    const int warp = threadIdx.x / kTeam;
     double* sm = reinterpret_cast<double*>(smem + m.hot_bytes) + (size_t)warp * m.cell_doubles;
+    // keep the lane id and the cell base in registers: without this the compiler re-derives them
+    // from S2R / constant-bank loads at every use (14 % of the executed instructions, profiles/r1)
+    asm volatile("" : "+r"(lane));
+    asm volatile("" : "+l"(sm));
     LaneRegs<NP, NSLOT> regs;
     // Jacobian entries that no reaction touches stay zero for the whole launch
     for (int i = lane; i < (m.NA + 1) * m.ldj; i += kTeam) sm[m.off_J + i] = 0.0;

@@ -47,8 +47,8 @@ void jac_t(const DevMech& m, double T, double p, const double* Y, double inv_hg,
     double ysum;
     load_cell_state<NP, NSLOT>(m, sm.data(), regs.data(), 0, Y, 1, 0, T, p, ysum);
     setup_rate_constants(m, sm.data(), T, 0);
-    eval_wdot(m, sm.data(), sm.data() + m.off_c, sm.data() + m.off_vec, 0, true);
-    run_gather(m.jac, m.coef, sm.data() + m.off_dq, sm.data() + m.off_J, 0);
+    init_const_slots(m, sm.data(), 0);
+    eval_wdot<true>(m, sm.data(), sm.data() + m.off_c, sm.data() + m.off_vec, regs.data(), 0);
     const double* J = sm.data() + m.off_J;
     // dense J in caller order incl. the default-efficiency rank-one part and the special columns
     for (int i = 0; i < m.NA; ++i)
@@ -58,10 +58,14 @@ void jac_t(const DevMech& m, double T, double p, const double* Y, double inv_hg,
             Jout[m.perm[i] * m.N + m.perm[j]] = v;
         }
     if (Ainv_out) {
-        gj_invert<NP, NSLOT>(m, sm.data(), regs.data(), 0, inv_hg);
-        for (int i = 0; i < m.NA; ++i)
-            for (int j = 0; j < m.NA; ++j)
-                Ainv_out[i * m.NA + j] = regs[i % kTeam].a[i / kTeam][j] * regs[i % kTeam].invd[i / kTeam];
+        invert_matrix<NP, NSLOT>(m, sm.data(), regs.data(), 0, inv_hg);
+        // column j of the inverse = solve against the unit vector e_j (through the stage-0 slot)
+        double* vec = sm.data() + m.off_vec;
+        for (int j = 0; j < m.NA; ++j) {
+            for (int i = 0; i < NP; ++i) vec[i] = i == j ? 1.0 : 0.0;
+            solve_stage<NP, NSLOT>(m, sm.data(), regs.data(), 0, vec, 0);
+            for (int i = 0; i < m.NA; ++i) Ainv_out[i * m.NA + j] = regs[i % kTeam].k[0][i / kTeam];
+        }
     }
 }
 }  // namespace
@@ -82,7 +86,7 @@ void emu_destroy(void* h) { delete static_cast<Emu*>(h); }
 void emu_info(void* h, int* out) {
     const DevMech& m = static_cast<Emu*>(h)->dm;
     int v[] = {m.N, m.NA, m.NP, m.R, m.n_msets, m.n_fall, m.n_pow, m.n_dq, m.n_part, m.cell_doubles,
-               m.wdotA.n_iter, m.wdotB.n_iter, m.jac.n_iter, static_cast<Emu*>(h)->ht.jac_entries,
+               m.wdotA.nA + m.wdotA.nB, m.msets.nA + m.msets.nB, m.jac.nA + m.jac.nB, static_cast<Emu*>(h)->ht.jac_entries,
                static_cast<Emu*>(h)->ht.wdot_entries};
     std::memcpy(out, v, sizeof(v));
 }

@@ -46,8 +46,9 @@ def test_conservation_and_determinism_at_scale(api, name, n):
     assert (np.abs(el) <= 1e-8 * ((np.abs(comp) / W[:, None]).T @ np.abs(RRn)) + floor[None] / W.min()).all()
     assert np.allclose(Q, -(h.hc[:, None] * RR).sum(0), rtol=1e-9, atol=1e-9 * np.abs(Q).max())
     assert cost.min() >= 1 and cost.max() < 5000
-    cold = b["T"] < 500.0
-    assert (cost[cold] <= 2).all()                         # nothing happens in cold cells: one step
+    # nothing happens in cold fuel/air cells (no radicals: the unburnt half of the batch): one step
+    cold = (b["T"] < 500.0) & ((b["Y"] > 0).sum(0) <= 4)
+    assert cold.sum() > 0 and (cost[cold] <= 2).all()
     RR2, Q2 = h.solve(b["T"], b["p"], b["rho"], 1e-6, b["Y"])
     assert np.array_equal(RR, RR2) and np.array_equal(Q, Q2)
     # RR is linear in the caller's density (it only scales the result, dfChemistryModel.C:770)
