@@ -168,9 +168,7 @@ DevMech HostTables::rebase(const void* base) const {
     d.coef = shift(d.coef, base);
     d.msets.ent = shift(d.msets.ent, base);
     d.msets.dst = shift(d.msets.dst, base);
-    d.wdotA.ent = shift(d.wdotA.ent, base);
-    d.wdotA.dst = shift(d.wdotA.dst, base);
-    d.wdotB = shift(d.wdotB, base);
+    d.wdot.tab = shift(d.wdot.tab, base);
     d.jac.ent = shift(d.jac.ent, base);
     d.jac.dst = shift(d.jac.dst, base);
     return d;
@@ -382,32 +380,7 @@ HostTables build_tables(const Mechanism& m) {
         if (mrows.back().b.empty()) mrows.back().b.push_back(U4{0, 0, 0, 0});  // M_s = 0 must still be stored
     }
     HostRowProg progM = pack_rows(mrows, std::max(n_msets, 1));
-    // wdot stage A: every row of a species is its own partial sum (rows spread evenly over the
-    // lanes); stage B adds each species' contiguous partials
-    std::vector<TargetRows> arows;
-    std::vector<uint32_t> wdotB(NP, 0u);
-    int n_part = 0;
-    for (int i = 0; i < NA; ++i) {
-        ht.wdot_entries += (int)wt[i].e.size();
-        GTarget t = wt[i];
-        TargetRows tr = make_rows(t, ct, R);
-        const int first = n_part;
-        for (const U4& r : tr.a) {
-            TargetRows one;
-            one.dst = n_part++;
-            one.a.push_back(r);
-            arows.push_back(one);
-        }
-        for (const U4& r : tr.b) {
-            TargetRows one;
-            one.dst = n_part++;
-            one.b.push_back(r);
-            arows.push_back(one);
-        }
-        if (n_part - first > 0xFFFF || first > 0xFFFF) throw std::runtime_error("tables: too many wdot partial sums");
-        wdotB[i] = (uint32_t)first | ((uint32_t)(n_part - first) << 16);
-    }
-    HostRowProg progA = pack_rows(arows, std::max(n_part, 1));
+    // (wdot schedule: built after the layout below, it needs the cell offsets)
     std::vector<TargetRows> jrows;
     for (auto& kv : jt) {
         ht.jac_entries += (int)kv.second.e.size();
@@ -418,6 +391,7 @@ HostTables build_tables(const Mechanism& m) {
     // ---- per-cell shared-memory layout (doubles; every offset even for 16-byte access) -----
     DevMech& L = ht.layout;
     L.N = N; L.NA = NA; L.NP = NP; L.R = R; L.n_msets = n_msets; L.n_fall = n_fall; L.n_pow = n_pow;
+    const int n_part = 4 * std::max(NA, 1);  // at most four partial sums per species
     L.n_dq = n_dq; L.n_part = n_part; L.ldj = ldj;
     int off = 0;
     auto take = [&](int n) { int o = off; off += (n + 1) & ~1; return o; };
@@ -440,8 +414,101 @@ HostTables build_tables(const Mechanism& m) {
         L.off_row = o;
     }
     L.off_J = take((NA + 1) * ldj);
-    L.off_red = 0;  // unused (team sums go through warp shuffles)
+    L.off_red = take(kTeam);  // dump slots of the wdot schedule
     L.cell_doubles = off;
+
+    // ---- wdot schedule (see WdotProg) ------------------------------------------------------
+    std::vector<uint16_t> wtab;
+    int wnA = 0, wnB = 0;
+    {
+        struct WRow { uint16_t s[4]; uint16_t dst; uint16_t flags; };
+        const uint16_t zero = (uint16_t)(L.off_q + R);
+        // rows of each species: [+,+,-,-]
+        std::vector<std::vector<WRow>> srows(NA);
+        for (int i = 0; i < NA; ++i) {
+            std::vector<uint16_t> pos, neg;
+            for (const GEntry& e : wt[i].e) {
+                ht.wdot_entries += 1;
+                const double ac = std::fabs(e.coef);
+                if (ac != std::round(ac) || ac > 32.0)
+                    throw std::runtime_error("tables: non-integer net stoichiometric coefficients are not supported");
+                for (int k = 0; k < (int)ac; ++k) (e.coef > 0 ? pos : neg).push_back((uint16_t)(L.off_q + e.src));
+            }
+            const size_t nr = std::max((pos.size() + 1) / 2, (neg.size() + 1) / 2);
+            for (size_t r2 = 0; r2 < nr; ++r2) {
+                WRow w;
+                for (int k = 0; k < 2; ++k) {
+                    w.s[k] = 2 * r2 + k < pos.size() ? pos[2 * r2 + k] : zero;
+                    w.s[2 + k] = 2 * r2 + k < neg.size() ? neg[2 * r2 + k] : zero;
+                }
+                w.dst = 0;
+                w.flags = 0;
+                srows[i].push_back(w);
+            }
+        }
+        // split every species into <= 4 groups of consecutive rows; a group = one partial sum on one lane
+        struct Group { int species, part; std::vector<WRow> rows; };
+        std::vector<Group> groups;
+        std::vector<std::vector<int>> parts_of(NA);
+        for (int i = 0; i < NA; ++i) {
+            // exactly four partial sums per species (all-zero rows pad the short ones): stage B is then
+            // the fixed pattern w_i = part[4i] + part[4i+1] + part[4i+2] + part[4i+3]
+            while (srows[i].size() < 4) {
+                WRow w;
+                for (int k = 0; k < 4; ++k) w.s[k] = zero;
+                w.dst = 0;
+                w.flags = 0;
+                srows[i].push_back(w);
+            }
+            const int nr = (int)srows[i].size();
+            const int ng = 4;
+            for (int gI = 0; gI < ng; ++gI) {
+                Group G;
+                G.species = i;
+                G.part = 4 * i + gI;
+                const int lo = nr * gI / ng, hi = nr * (gI + 1) / ng;
+                G.rows.assign(srows[i].begin() + lo, srows[i].begin() + hi);
+                parts_of[i].push_back(G.part);
+                groups.push_back(G);
+            }
+        }
+        std::stable_sort(groups.begin(), groups.end(),
+                         [](const Group& x, const Group& y) { return x.rows.size() > y.rows.size(); });
+        std::vector<std::vector<WRow>> laneA(kTeam), laneB(kTeam);
+        for (const Group& G : groups) {
+            int best = 0;
+            for (int l = 1; l < kTeam; ++l)
+                if (laneA[l].size() < laneA[best].size()) best = l;
+            for (size_t r2 = 0; r2 < G.rows.size(); ++r2) {
+                WRow w = G.rows[r2];
+                w.flags = r2 == 0 ? 1 : 0;
+                w.dst = r2 + 1 == G.rows.size() ? (uint16_t)(L.off_part + G.part) : (uint16_t)(L.off_red + best);
+                laneA[best].push_back(w);
+            }
+        }
+        for (int l = 0; l < kTeam; ++l) {
+            wnA = std::max(wnA, (int)laneA[l].size());
+            wnB = std::max(wnB, (int)laneB[l].size());
+        }
+        if (wnA > kWdotRowsMax)
+            throw std::runtime_error("tables: wdot schedule exceeds the register budget of the kernels");
+        if (off > 0xFFFF) throw std::runtime_error("tables: per-cell block too large for 16-bit offsets");
+        wtab.assign((size_t)(wnA + wnB) * kTeam * 6, 0);
+        auto put = [&](int row, int l, const WRow& w) {
+            uint16_t* t = &wtab[((size_t)row * kTeam + l) * 6];
+            for (int k = 0; k < 4; ++k) t[k] = w.s[k];
+            t[4] = w.dst;
+            t[5] = w.flags;
+        };
+        WRow idle;
+        for (int k = 0; k < 4; ++k) idle.s[k] = zero;
+        idle.flags = 1;
+        for (int l = 0; l < kTeam; ++l) {
+            idle.dst = (uint16_t)(L.off_red + l);
+            for (int r2 = 0; r2 < wnA; ++r2) put(r2, l, r2 < (int)laneA[l].size() ? laneA[l][r2] : idle);
+            for (int r2 = 0; r2 < wnB; ++r2) put(wnA + r2, l, r2 < (int)laneB[l].size() ? laneB[l][r2] : idle);
+        }
+    }
 
     // ---- blob ------------------------------------------------------------------------------
     Blob B;
@@ -456,8 +523,6 @@ HostTables build_tables(const Mechanism& m) {
         out.dst = as_ptr<uint32_t>(B.add(hp.dst));
     };
     add_prog(progM, L.msets);
-    add_prog(progA, L.wdotA);
-    L.wdotB = as_ptr<uint32_t>(B.add(wdotB));
     add_prog(progJ, L.jac);
     L.hot_base = as_ptr<uint8_t>(0);
     L.hot_bytes = (int)((B.b.size() + 15) & ~size_t(15));
@@ -470,6 +535,9 @@ HostTables build_tables(const Mechanism& m) {
     L.arrh = as_ptr<double>(B.add(arrh));
     L.fall = as_ptr<double>(B.add(fall));
     L.powtab = as_ptr<double>(B.add(powtab));
+    L.wdot.nA = wnA;
+    L.wdot.nB = wnB;
+    L.wdot.tab = as_ptr<uint16_t>(B.add(wtab));
     ht.blob = std::move(B.b);
     return ht;
 }

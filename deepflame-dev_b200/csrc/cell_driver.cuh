@@ -143,7 +143,7 @@ DFC_HD void wdot_one_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* reg
     load_cell_state<NP, NSLOT>(m, sm, regs, dfc_lane, Y, ldY, cell, Tc, p[cell], ysum);
     setup_rate_constants(m, sm, Tc, dfc_lane);
     init_const_slots(m, sm, dfc_lane);
-    eval_wdot<false>(m, sm, sm + m.off_c, sm + m.off_vec, regs, dfc_lane);
+    eval_wdot<false>(m, sm, sm + m.off_c, regs, dfc_lane);
     DFC_LANES_BEGIN
     for (int k = tl; k < m.N; k += kTeam)
         wr[(size_t)DFC_LDG(m.perm + k) * ldW + cell] = k < m.NA ? sm[m.off_vec + k] * DFC_LDG(m.W + k) : 0.0;

@@ -100,6 +100,8 @@ DFC_HD double rodas_c(int i, int j) {
 // Matrices with 33..36 rows use the bordered layout (integrator.cuh): 32 core rows, one per lane,
 // and NB = NP - 32 border rows handled through the Schur complement.
 constexpr int border_rows(int NP) { return (NP > 32 && NP <= 36) ? NP - 32 : 0; }
+// stage-A rows of the wdot schedule a lane can keep in registers (WdotProg), by kernel size class
+constexpr int wdot_rows_cap(int NP) { return NP <= 16 ? 4 : NP <= 24 ? 6 : NP <= 36 ? 10 : kWdotRowsMax; }
 
 template <int NP, int NSLOT>
 struct LaneRegs {
@@ -120,6 +122,9 @@ struct LaneRegs {
     double f0[NSLOT];         // wdot at the step's base point
     double inc[NSLOT];        // increment of the step being tested
     double red;               // this lane's term of a team reduction (team_sum)
+    // this lane's rows of the wdot schedule: byte offsets of s0..s3 and dst (load_wdot_regs)
+    static constexpr int RW = wdot_rows_cap(NP);
+    uint32_t wa[RW][5];       // [4]: dst offset | bit 31 = the row starts a new partial sum
 };
 
 struct D2 {
@@ -168,9 +173,6 @@ DFC_HD DevMech rebase_hot(const DevMech& m, const uint8_t* nb) {
     DFC_REBASE(coef, double);
     DFC_REBASE(msets.ent, U4);
     DFC_REBASE(msets.dst, uint32_t);
-    DFC_REBASE(wdotA.ent, U4);
-    DFC_REBASE(wdotA.dst, uint32_t);
-    DFC_REBASE(wdotB, uint32_t);
     DFC_REBASE(jac.ent, U4);
     DFC_REBASE(jac.dst, uint32_t);
 #undef DFC_REBASE
@@ -240,6 +242,68 @@ DFC_HD void team_sum_n(Regs* regs, double* z) {
         z[b] = t[0];
     }
 #endif
+}
+
+// ---- register-resident wdot schedule (see WdotProg) ------------------------------------------
+// Offsets are bytes from `DFC_SMEM_BASE`: the CTA's dynamic shared memory on the device (so the
+// compiler emits LDS/STS with the offset register as the whole address), the cell block in the
+// host emulation.
+#ifdef __CUDA_ARCH__
+extern __shared__ double2 dfc_smem[];
+#define DFC_SMEM_BASE(sm) reinterpret_cast<char*>(dfc_smem)
+#else
+#define DFC_SMEM_BASE(sm) reinterpret_cast<char*>(sm)
+#endif
+DFC_HD double ldo(const char* base, uint32_t off) { return *reinterpret_cast<const double*>(base + off); }
+DFC_HD void sto(char* base, uint32_t off, double v) { *reinterpret_cast<double*>(base + off) = v; }
+
+// cell_off: byte offset of this team's cell block from DFC_SMEM_BASE (0 in the emulation)
+template <class Regs>
+DFC_HD bool load_wdot_regs(const DevMech& m, Regs* regs, int dfc_lane, uint32_t cell_off) {
+    (void)dfc_lane;
+    if (m.wdot.nA > Regs::RW) return false;
+    DFC_LANES_BEGIN
+    DFC_UNROLL
+    for (int i = 0; i < Regs::RW; ++i) {
+        DFC_UNROLL
+        for (int k = 0; k < 5; ++k) DFC_LR.wa[i][k] = 0;
+        if (i < m.wdot.nA) {
+            const uint16_t* t = m.wdot.tab + ((size_t)i * kTeam + tl) * 6;
+            DFC_UNROLL
+            for (int k = 0; k < 5; ++k) DFC_LR.wa[i][k] = cell_off + 8u * DFC_LDG(t + k);
+            DFC_LR.wa[i][4] |= (uint32_t)(DFC_LDG(t + 5) & 1u) << 31;
+        }
+    }
+    DFC_LANES_END
+    return true;
+}
+
+// w = S q: q[R+1] -> part[4 NA] -> vec[0..NA)
+template <class Regs>
+DFC_HD void run_wdot(const DevMech& m, double* sm, Regs* regs, int dfc_lane) {
+    (void)dfc_lane;
+    char* base = DFC_SMEM_BASE(sm);
+    DFC_LANES_BEGIN
+    double acc = 0.0;
+    DFC_UNROLL
+    for (int i = 0; i < Regs::RW; ++i) {
+        if (i < m.wdot.nA) {
+            const double s = (ldo(base, DFC_LR.wa[i][0]) + ldo(base, DFC_LR.wa[i][1])) -
+                             (ldo(base, DFC_LR.wa[i][2]) + ldo(base, DFC_LR.wa[i][3]));
+            const uint32_t d = DFC_LR.wa[i][4];
+            acc = ((int32_t)d < 0) ? s : acc + s;
+            sto(base, d & 0x7FFFFFFFu, acc);
+        }
+    }
+    DFC_LANES_END
+    const double* part = sm + m.off_part;
+    double* vec = sm + m.off_vec;
+    DFC_LANES_BEGIN
+    for (int i = tl; i < m.NA; i += kTeam) {
+        const D2 p0 = ld2(part + 4 * i), p1 = ld2(part + 4 * i + 2);
+        vec[i] = (p0.x + p0.y) + (p1.x + p1.y);
+    }
+    DFC_LANES_END
 }
 
 // ---- row programs (see RowProg) ---------------------------------------------------------------
@@ -388,10 +452,10 @@ DFC_HD void eval_reactions(const DevMech& m, double* sm, const double* cx, int d
     DFC_LANES_END
 }
 
-// wdot_i (i < NA) at concentrations cx -> out[i].  cx is one of the cell's c / cs arrays
-// ([N + 2]: slot N = 1.0, slot N+1 receives the total concentration).
+// wdot_i (i < NA) at concentrations cx -> vec[i] (sm + off_vec).  cx is one of the cell's c / cs
+// arrays ([N + 2]: slot N = 1.0, slot N+1 receives the total concentration).
 template <bool JAC, class Regs>
-DFC_HD void eval_wdot(const DevMech& m, double* sm, double* cx, double* out, Regs* regs, int dfc_lane) {
+DFC_HD void eval_wdot(const DevMech& m, double* sm, double* cx, Regs* regs, int dfc_lane) {
     (void)dfc_lane;
     if (m.n_msets > 0) {
         DFC_LANES_BEGIN
@@ -414,23 +478,7 @@ DFC_HD void eval_wdot(const DevMech& m, double* sm, double* cx, double* out, Reg
     eval_reactions<JAC>(m, sm, cx, dfc_lane);
     // J = d wdot / d c from the reaction derivatives; must run before part/out overwrite dq
     if (JAC) run_rows(m.jac, m.coef, sm + m.off_dq, sm + m.off_J, dfc_lane);
-    run_rows(m.wdotA, m.coef, sm + m.off_q, sm + m.off_part, dfc_lane);
-    const double* part = sm + m.off_part;
-    DFC_LANES_BEGIN
-    for (int i = tl; i < m.NA; i += kTeam) {
-        const uint32_t w = m.wdotB[i];
-        const double* p = part + (w & 0xFFFFu);
-        const int n = (int)(w >> 16);
-        double s0 = 0.0, s1 = 0.0;
-        int j = 0;
-        for (; j + 1 < n; j += 2) {
-            s0 += p[j];
-            s1 += p[j + 1];
-        }
-        if (j < n) s0 += p[j];
-        out[i] = s0 + s1;
-    }
-    DFC_LANES_END
+    run_wdot(m, sm, regs, dfc_lane);
 }
 
 // ---- per-cell constants of the frozen-T sub-step: kf, 1/Kc, falloff k0/kinf and log10 Fcent ---

@@ -56,13 +56,29 @@ struct RowProg {
 //                d q/d[M] (three-body / falloff only)
 constexpr uint32_t kFlagRev = 4u, kFlagPow = 1u << 27;
 
+// wdot = S q as a register-resident schedule: every lane keeps its rows' shared-memory offsets in
+// registers for the whole launch (they are constants of the mechanism), so a row costs four
+// loads, four adds and a store with no decoding.  Row = (q[s0] + q[s1]) - (q[s2] + q[s3]); integer
+// stoichiometric coefficients are expanded into repeated entries and unused slots point at a
+// slot that holds 0.0.  Stage A rows accumulate into at most four partial sums per species
+// (consecutive rows of one partial sit on one lane); every species has exactly four partials,
+// part[4i .. 4i+3], so stage B is the fixed pattern w_i = their sum and needs no table.
+// Table record (uint16 x 6) per (row, lane): s0..s3 and dst = double index relative to the cell
+// base, flags: bit0 = start a new partial (reset the accumulator).  Rows that do not finish a
+// partial store to the lane's dump slot.
+struct WdotProg {
+    int nA, nB;            // stage-A rows per lane (nB unused, 0)
+    const uint16_t* tab;   // [nA * kTeam * 6]
+};
+constexpr int kWdotRowsMax = 16;
+
 struct DevMech {
     int N, NA, NP, R, n_msets, n_fall, n_pow, n_dq, n_part, ldj;  // NP: padded NA (kernel template)
     // per-cell shared-memory layout, offsets in doubles from the cell's base (all even)
     // c, cs: [N + 2] concentrations, slot N = 1.0 (absent factor), slot N+1 = sum of all N
     // kf: [2R] interleaved (kf_r, 1/Kc_r);  q: [R + 1], slot R = 0.0;  dq: [n_dq + 1], last = 0.0
     int off_c, off_cs, off_kf, off_k0, off_lfc, off_M, off_q, off_dq, off_J, off_vec,
-        off_row, off_part, off_red, cell_doubles;
+        off_row, off_part, off_red, cell_doubles;  // off_red: kTeam dump slots
     // hot tables (rdesc, coef, row programs) are one contiguous prefix of the
     // table blob; the kernels stage it in shared memory once per CTA (rebase_hot)
     const uint8_t* hot_base;
@@ -82,8 +98,7 @@ struct DevMech {
     // row programs
     const double* coef;    // distinct coefficients, coef[0] = 0
     RowProg msets;         // c[N+2] -> M[n_msets]
-    RowProg wdotA;         // q[R+1] -> part[n_part]  (each species' partial sums are contiguous)
-    const uint32_t* wdotB; // [NP] first partial | count << 16 : w_i = sum of its partials
+    WdotProg wdot;         // q[R+1] -> part[n_part] -> w[NA]  (cold table: read once per launch)
     RowProg jac;           // dq[n_dq+1] -> J[(NA+1)*ldj]; column NA holds gsum_i = sum_r nu_ir dflt_r dq_r/d[M]
 };
 

@@ -74,6 +74,7 @@ size_t smem_bytes(const dfchem_ctx* h) {
 
 template <int NP, int NSLOT>
 cudaError_t configure_t(dfchem_ctx* h) {
+    if (h->dm.wdot.nA > wdot_rows_cap(NP)) return cudaErrorLaunchOutOfResources;
     int max_optin = 0;
     cudaError_t e = cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
     if (e != cudaSuccess) return e;

@@ -366,7 +366,7 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
     bool after_reject = false;
     while (true) {
         // base point: f0 = wdot(c), J = d wdot/d c (eval_wdot<true> also runs the Jacobian rows)
-        eval_wdot<true>(m, sm, c, vec, regs, dfc_lane);
+        eval_wdot<true>(m, sm, c, regs, dfc_lane);
         DFC_LANES_BEGIN
         DFC_UNROLL
         for (int s = 0; s < NSLOT; ++s) {
@@ -404,7 +404,7 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
                         if (row < NA) cs[row] = stage_point<NSLOT>(i, DFC_LR.k, s, c[row]);
                     }
                     DFC_LANES_END
-                    eval_wdot<false>(m, sm, cs, vec, regs, dfc_lane);
+                    eval_wdot<false>(m, sm, cs, regs, dfc_lane);
                 }
                 DFC_LANES_BEGIN
                 DFC_UNROLL

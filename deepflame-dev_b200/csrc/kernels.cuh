@@ -28,12 +28,15 @@ solve_kernel(const DevMech mg, const SolveArgs a, unsigned int* queue, unsigned 
     const DevMech m = stage_hot_tables(mg, smem);
     int lane = threadIdx.x % kTeam;
     const int warp = threadIdx.x / kTeam;
-    double* sm = reinterpret_cast<double*>(smem + m.hot_bytes) + (size_t)warp * m.cell_doubles;
-    // keep the lane id and the cell base in registers: without this the compiler re-derives them
-    // from S2R / constant-bank loads at every use (14 % of the executed instructions, profiles/r1)
+    // keep the lane id and the cell block's shared-memory offset in registers: without this the
+    // compiler re-derives them from S2R / constant-bank loads at every use (14 % of the executed
+    // instructions, profiles/r1); the offset stays an integer so that accesses remain LDS/STS
+    uint32_t cell_off = (uint32_t)m.hot_bytes + (uint32_t)warp * (uint32_t)m.cell_doubles * 8u;
     asm volatile("" : "+r"(lane));
-    asm volatile("" : "+l"(sm));
+    asm volatile("" : "+r"(cell_off));
+    double* sm = reinterpret_cast<double*>(smem + cell_off);
     LaneRegs<NP, NSLOT> regs;
+    load_wdot_regs(m, &regs, lane, cell_off);
     // Jacobian entries that no reaction touches stay zero for the whole launch
     for (int i = lane; i < (m.NA + 1) * m.ldj; i += kTeam) sm[m.off_J + i] = 0.0;
     __syncwarp();
@@ -65,8 +68,10 @@ wdot_kernel(const DevMech mg, int nC, const double* T, const double* p, const do
     unsigned char* smem = reinterpret_cast<unsigned char*>(dfc_smem);
     const DevMech m = stage_hot_tables(mg, smem);
     const int lane = threadIdx.x % kTeam, warp = threadIdx.x / kTeam;
-    double* sm = reinterpret_cast<double*>(smem + m.hot_bytes) + (size_t)warp * m.cell_doubles;
+    const uint32_t cell_off = (uint32_t)m.hot_bytes + (uint32_t)warp * (uint32_t)m.cell_doubles * 8u;
+    double* sm = reinterpret_cast<double*>(smem + cell_off);
     LaneRegs<NP, NSLOT> regs;
+    load_wdot_regs(m, &regs, lane, cell_off);
     while (true) {
         int cell = 0;
         if (lane == 0) cell = (int)atomicAdd(queue, 1u);

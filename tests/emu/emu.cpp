@@ -21,6 +21,7 @@ template <int NP, int NSLOT>
 void solve_t(const DevMech& m, const SolveArgs& a, unsigned long long* counters) {
     std::vector<double> sm(m.cell_doubles, 0.0);
     std::vector<LaneRegs<NP, NSLOT>> regs(kTeam);
+    if (!load_wdot_regs(m, regs.data(), 0, 0u)) throw std::runtime_error("wdot schedule too large");
     for (int cell = 0; cell < a.nC; ++cell) {
         std::fill(sm.begin(), sm.end(), 0.0);
         StepStats st;
@@ -35,6 +36,7 @@ void wdot_t(const DevMech& m, int nC, const double* T, const double* p, const do
             double* wr, int ldW) {
     std::vector<double> sm(m.cell_doubles, 0.0);
     std::vector<LaneRegs<NP, NSLOT>> regs(kTeam);
+    if (!load_wdot_regs(m, regs.data(), 0, 0u)) throw std::runtime_error("wdot schedule too large");
     for (int cell = 0; cell < nC; ++cell)
         wdot_one_cell<NP, NSLOT>(m, sm.data(), regs.data(), 0, T, p, Y, ldY, wr, ldW, cell);
 }
@@ -44,11 +46,12 @@ void jac_t(const DevMech& m, double T, double p, const double* Y, double inv_hg,
            double* Ainv_out) {
     std::vector<double> sm(m.cell_doubles, 0.0);
     std::vector<LaneRegs<NP, NSLOT>> regs(kTeam);
+    if (!load_wdot_regs(m, regs.data(), 0, 0u)) throw std::runtime_error("wdot schedule too large");
     double ysum;
     load_cell_state<NP, NSLOT>(m, sm.data(), regs.data(), 0, Y, 1, 0, T, p, ysum);
     setup_rate_constants(m, sm.data(), T, 0);
     init_const_slots(m, sm.data(), 0);
-    eval_wdot<true>(m, sm.data(), sm.data() + m.off_c, sm.data() + m.off_vec, regs.data(), 0);
+    eval_wdot<true>(m, sm.data(), sm.data() + m.off_c, regs.data(), 0);
     const double* J = sm.data() + m.off_J;
     // dense J in caller order incl. the default-efficiency rank-one part and the special columns
     for (int i = 0; i < m.NA; ++i)
@@ -86,7 +89,7 @@ void emu_destroy(void* h) { delete static_cast<Emu*>(h); }
 void emu_info(void* h, int* out) {
     const DevMech& m = static_cast<Emu*>(h)->dm;
     int v[] = {m.N, m.NA, m.NP, m.R, m.n_msets, m.n_fall, m.n_pow, m.n_dq, m.n_part, m.cell_doubles,
-               m.wdotA.nA + m.wdotA.nB, m.msets.nA + m.msets.nB, m.jac.nA + m.jac.nB, static_cast<Emu*>(h)->ht.jac_entries,
+               m.wdot.nA, m.msets.nA + m.msets.nB, m.jac.nA + m.jac.nB, static_cast<Emu*>(h)->ht.jac_entries,
                static_cast<Emu*>(h)->ht.wdot_entries};
     std::memcpy(out, v, sizeof(v));
 }
