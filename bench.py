@@ -177,6 +177,12 @@ def main():
     ap.add_argument("--dt", type=float, default=1e-6)
     ap.add_argument("--ref-cells", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-thermo", action="store_true", help="skip the correctThermo (HBM-bound) leg")
+    ap.add_argument("--thermo-only", action="store_true", help="run only the correctThermo leg (ncu captures)")
+    ap.add_argument("--skew", type=float, default=0.0,
+                    help="make rank loads unequal: rank r draws T from [300 + skew*r*200, 2500] K (N > 1)")
+    ap.add_argument("--rebalance", action="store_true",
+                    help="cost-weighted all-to-all-v of cells between ranks before each step (N > 1)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -199,7 +205,8 @@ def main():
     h = dfchem_host.Handle(synth.load_blob(args.mech), local)
     h.set_tolerances(args.rtol, args.atol)
     n = args.cells
-    batch = synth.make_batch(args.mech, h.species, h.W, n, seed=12345 + rank)
+    T_range = (300.0 + args.skew * rank * 200.0, 2500.0) if args.skew else (300.0, 2500.0)
+    batch = synth.make_batch(args.mech, h.species, h.W, n, seed=12345 + rank, T_range=T_range)
     N = h.N
 
     # ---- device-resident arm -------------------------------------------------------------
@@ -215,6 +222,30 @@ def main():
                                      d["Y"].data_ptr(), n, dRR.data_ptr(), n, dQ.data_ptr(), dcost.data_ptr(),
                                      dstat.data_ptr(), stream.cuda_stream))
 
+    rb = None
+    if args.rebalance and world > 1:
+        from dfchem_host import balance
+
+        rb = balance.Rebalancer()
+        fields = torch.cat([d["T"][None], d["p"][None], d["rho"][None], d["Y"]], 0).contiguous()   # [N + 3, n]
+        step_dev()                                   # cost of the previous flow step = the balancer's input
+        torch.cuda.synchronize()
+        prev_cost = dcost.clone()
+
+        def solve_block(block):
+            nb = block.shape[1]
+            block = block.contiguous()
+            res = torch.empty((N + 2, nb), dtype=torch.float64, device=dev)
+            h.check(lib.dfchem_solve_dev(h.h, nb, block[0].data_ptr(), block[1].data_ptr(), block[2].data_ptr(), None,
+                                         args.dt, block[3].data_ptr(), nb, res.data_ptr(), nb, res[N].data_ptr(),
+                                         res[N + 1].data_ptr(), None, stream.cuda_stream))
+            return res
+
+        def step_dev():  # noqa: F811  (balanced variant replaces the plain step)
+            out, _ = balance.solve_balanced(rb, solve_block, fields, prev_cost, N + 2)
+            dRR.copy_(out[:N])
+            dQ.copy_(out[N])
+
     def barrier():
         torch.cuda.synchronize()
         if world > 1:
@@ -227,6 +258,55 @@ def main():
         t = torch.tensor([x], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
+
+    def thermo_leg():
+    # ---- correctThermo leg (HBM-bound): T from (h, p, Y), psi, rho [+ cp, hai] ------------------
+        thermo = None
+        if not args.no_thermo:
+            he = torch.empty(n, dtype=torch.float64, device=dev)
+            h.check(lib.dfchem_h_from_T_dev(h.h, n, d["T"].data_ptr(), d["Y"].data_ptr(), n, he.data_ptr(), stream.cuda_stream))
+            Tg = (d["T"] + 30.0).contiguous()                      # a flow step moves T by tens of K at most
+            Tw = torch.empty_like(Tg)
+            psi, rho2, cpo = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(3))
+            hai = torch.empty((N, n), dtype=torch.float64, device=dev)
+            thermo = {}
+            for label, cp_ptr, hai_ptr, nbytes in (("T_psi_rho", None, None, (N + 3) * 8 + 3 * 8),
+                                                   ("T_psi_rho_cp_hai", cpo.data_ptr(), hai.data_ptr(), (N + 3) * 8 + (4 + N) * 8)):
+                def step_thermo():
+                    Tw.copy_(Tg)                                   # in/out argument: restore the guess (counted in the bytes)
+                    h.check(lib.dfchem_correct_thermo_dev(h.h, n, he.data_ptr(), d["p"].data_ptr(), d["Y"].data_ptr(), n,
+                                                          Tw.data_ptr(), psi.data_ptr(), rho2.data_ptr(), cp_ptr, hai_ptr, n,
+                                                          stream.cuda_stream))
+                for _ in range(3):
+                    step_thermo()
+                barrier()
+                reps = 10
+                t0e, t1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                tc0, tc1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                tc0.record(stream)
+                for _ in range(reps):
+                    Tw.copy_(Tg)
+                tc1.record(stream)
+                t0e.record(stream)
+                for _ in range(reps):
+                    step_thermo()
+                t1e.record(stream)
+                barrier()
+                ms_t = (t0e.elapsed_time(t1e) - tc0.elapsed_time(tc1)) / reps   # kernel alone (copy of the guess subtracted)
+                ms_t = max_over_ranks(ms_t)
+                err = float((Tw - d["T"]).abs().max().item())
+                thermo[label] = {"cells_per_s": world * n / (ms_t * 1e-3), "ms": ms_t, "algorithmic_bytes_per_cell": nbytes,
+                                 "achieved_GBps": nbytes * n / (ms_t * 1e-3) / 1e9, "max_abs_T_error_K": err}
+            del hai
+        return thermo
+
+    if args.thermo_only:
+        th = thermo_leg()
+        if rank == 0:
+            print(json.dumps({"thermo": th, "n_gpus": world, "cells_per_gpu": n}), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     for _ in range(args.warmup):
         step_dev()
@@ -271,6 +351,8 @@ def main():
            "h2d_bytes_per_step": (N + 3) * n * 8, "d2h_bytes_per_step": (N + 1) * n * 8,
            "matches_device_arm": same}
 
+    thermo = thermo_leg()
+
     if rank == 0:
         pk = ctypes.c_double()
         rc = lib.dfchem_bench_fp64_peak(local, ctypes.byref(pk))
@@ -281,7 +363,8 @@ def main():
         tfile = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tfile):
             try:
-                traffic = json.load(open(tfile)).get(args.mech)
+                rec = json.load(open(tfile)).get(args.mech)
+                traffic = rec["dram_bytes_per_cell"] * n if rec else None   # per launch, scaled from the ncu capture
             except (OSError, ValueError):
                 traffic = None
         roof = {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
@@ -293,10 +376,21 @@ def main():
         out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                "data": "synthetic", "config": workload_config(args, n), "clocks": clocks, "e2e": e2e,
-               "gpu_launches": args.steps * 1, "roofline": roof,
+               "gpu_launches": args.steps * 1, "roofline": roof, "rebalance": bool(rb), "skew": args.skew,
                "integrator_stats": {"accepted_steps": cnt["accepted"], "rejected_steps": cnt["rejected"],
                                     "mean_attempts_per_cell": cost_mean, "max_attempts_per_cell": cost_max,
                                     "failed_cells": failed}}
+        if thermo is not None:
+            hbm = None
+            try:
+                hbm = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+                src = "MEASURED_PEAKS.json hbm_gbs (measured copy bandwidth)"
+            except (OSError, KeyError, ValueError):
+                hbm, src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+            for v in thermo.values():
+                v["roofline"] = {"bound": "hbm", "achieved": v["achieved_GBps"], "peak": hbm, "unit": "GB/s",
+                                 "frac": v["achieved_GBps"] / hbm, "peak_source": src, "kernel": "thermo_kernel"}
+            out["thermo"] = thermo
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             probe = min(n, 16 * threads)

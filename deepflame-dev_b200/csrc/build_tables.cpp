@@ -166,8 +166,8 @@ DevMech HostTables::rebase(const void* base) const {
     d.fall = shift(d.fall, base);
     d.powtab = shift(d.powtab, base);
     d.coef = shift(d.coef, base);
-    d.msets.ent = shift(d.msets.ent, base);
-    d.msets.dst = shift(d.msets.dst, base);
+    d.ms_ent = shift(d.ms_ent, base);
+    d.ms_rng = shift(d.ms_rng, base);
     d.wdot.tab = shift(d.wdot.tab, base);
     d.jac.ent = shift(d.jac.ent, base);
     d.jac.dst = shift(d.jac.dst, base);
@@ -369,17 +369,20 @@ HostTables build_tables(const Mechanism& m) {
     // ---- row programs ----------------------------------------------------------------------
     CoefTable ct;
     // third-body sets: M_s = dflt_s * ctot + sum_j (eff_sj - dflt_s) c_j ; ctot lives in slot N+1
-    std::vector<TargetRows> mrows;
+    std::vector<U4> ms_ent;
+    std::vector<uint32_t> ms_rng;
+    auto ms_push = [&](double val, int idx) {
+        uint32_t w[2];
+        std::memcpy(w, &val, 8);
+        ms_ent.push_back(U4{w[0], w[1], (uint32_t)idx * 8u, 0u});
+    };
     for (int sidx = 0; sidx < n_msets; ++sidx) {
-        GTarget t;
-        t.dst = sidx;
-        if (ms_dflt[sidx] != 0.0) t.e.push_back({N + 1, ms_dflt[sidx]});
-        for (int q = ms_ptr[sidx]; q < ms_ptr[sidx + 1]; ++q) t.e.push_back({ms_idx[q], ms_val[q]});
-        if (t.e.empty()) t.e.push_back({N + 1, 0.0});
-        mrows.push_back(make_rows(t, ct, -1));
-        if (mrows.back().b.empty()) mrows.back().b.push_back(U4{0, 0, 0, 0});  // M_s = 0 must still be stored
+        const size_t first = ms_ent.size();
+        if (ms_dflt[sidx] != 0.0) ms_push(ms_dflt[sidx], N + 1);
+        for (int q = ms_ptr[sidx]; q < ms_ptr[sidx + 1]; ++q) ms_push(ms_val[q], ms_idx[q]);
+        if (first > 0xFFFF) throw std::runtime_error("tables: efficiency table too large");
+        ms_rng.push_back((uint32_t)first | ((uint32_t)(ms_ent.size() - first) << 16));
     }
-    HostRowProg progM = pack_rows(mrows, std::max(n_msets, 1));
     // (wdot schedule: built after the layout below, it needs the cell offsets)
     std::vector<TargetRows> jrows;
     for (auto& kv : jt) {
@@ -400,7 +403,7 @@ HostTables build_tables(const Mechanism& m) {
     L.off_kf = take(2 * R);
     L.off_k0 = take(n_fall);
     L.off_lfc = take(n_fall);
-    L.off_M = take(n_msets);
+    L.off_M = 0;  // unused: every reaction lane evaluates its own third-body concentration
     L.off_q = take(R + 1);
     // dq is dead once the Jacobian row program has run (inside eval_wdot<true>, before the wdot
     // rows); the partial sums, the stage vector and the Gauss-Jordan pivot-row buffer reuse it
@@ -522,7 +525,8 @@ HostTables build_tables(const Mechanism& m) {
         out.ent = as_ptr<U4>(B.add(hp.ent));
         out.dst = as_ptr<uint32_t>(B.add(hp.dst));
     };
-    add_prog(progM, L.msets);
+    L.ms_ent = as_ptr<U4>(B.add(ms_ent));
+    L.ms_rng = as_ptr<uint32_t>(B.add(ms_rng));
     add_prog(progJ, L.jac);
     L.hot_base = as_ptr<uint8_t>(0);
     L.hot_bytes = (int)((B.b.size() + 15) & ~size_t(15));

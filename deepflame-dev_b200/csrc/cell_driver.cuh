@@ -60,8 +60,6 @@ DFC_HD double load_cell_state(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>*
     DFC_LANES_BEGIN
     DFC_UNROLL
     for (int s = 0; s < NSLOT; ++s) {
-        const int row = tl + kTeam * s;
-        DFC_LR.c0[s] = row < m.NA ? c[row] : 0.0;
         DFC_LR.dc[s] = 0.0;
     }
     DFC_LANES_END

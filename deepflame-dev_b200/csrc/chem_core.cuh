@@ -16,6 +16,7 @@
 // team-uniformly (every lane computes the same value from shared memory).
 #pragma once
 #include <cmath>
+#include <cstring>
 
 #include "dev_tables.hpp"
 
@@ -117,10 +118,8 @@ struct LaneRegs {
     double redv[NBX];         // bordered: this lane's terms of the border dot products
     double tmp;
     double k[kStages][NSLOT]; // stage increments
-    double c0[NSLOT];         // concentrations at t = 0
-    double dc[NSLOT];         // accumulated increment c(t) - c0 (kept separately: RR needs c - c0)
+    double dc[NSLOT];         // accumulated increment c(t) - c(0) (kept separately: RR needs c - c0)
     double f0[NSLOT];         // wdot at the step's base point
-    double inc[NSLOT];        // increment of the step being tested
     double red;               // this lane's term of a team reduction (team_sum)
     // this lane's rows of the wdot schedule: byte offsets of s0..s3 and dst (load_wdot_regs)
     static constexpr int RW = wdot_rows_cap(NP);
@@ -171,8 +170,8 @@ DFC_HD DevMech rebase_hot(const DevMech& m, const uint8_t* nb) {
     r.hot_base = nb;
     DFC_REBASE(rdesc, U4);
     DFC_REBASE(coef, double);
-    DFC_REBASE(msets.ent, U4);
-    DFC_REBASE(msets.dst, uint32_t);
+    DFC_REBASE(ms_ent, U4);
+    DFC_REBASE(ms_rng, uint32_t);
     DFC_REBASE(jac.ent, U4);
     DFC_REBASE(jac.dst, uint32_t);
 #undef DFC_REBASE
@@ -192,6 +191,16 @@ DFC_HD U4 ld_u4(const U4* p) {
     return U4{v.x, v.y, v.z, v.w};
 #else
     return *p;
+#endif
+}
+DFC_HD double u2d(uint32_t lo, uint32_t hi) {
+#ifdef __CUDA_ARCH__
+    return __hiloint2double((int)hi, (int)lo);
+#else
+    const uint64_t b = ((uint64_t)hi << 32) | lo;
+    double v;
+    memcpy(&v, &b, 8);
+    return v;
 #endif
 }
 // +/- v selected by bit 31 of the entry word (one LOP3 on the high half of the double)
@@ -407,7 +416,14 @@ DFC_HD void eval_reactions(const DevMech& m, double* sm, const double* cx, int d
         double kfe = kk.x;
         double dkdM = 0.0;
         if (kind != (uint32_t)kElementary) {
-            const double M = sm[m.off_M + (d.z & 0xFFu)];
+            // third-body concentration of this reaction's efficiency set
+            const uint32_t rg = m.ms_rng[d.z & 0xFFu];
+            const U4* me = m.ms_ent + (rg & 0xFFFFu);
+            double M = 0.0;
+            for (int t = 0, nt = (int)(rg >> 16); t < nt; ++t) {
+                const U4 u = ld_u4(me + t);
+                M = fma(u2d(u.x, u.y), ldb(cx, u.z), M);
+            }
             if (kind == (uint32_t)kThreeBody) {
                 dkdM = kfe;
                 kfe *= M;
@@ -467,7 +483,6 @@ DFC_HD void eval_wdot(const DevMech& m, double* sm, double* cx, Regs* regs, int 
         DFC_LANES_BEGIN
         if (tl == 0) cx[m.N + 1] = ctot;
         DFC_LANES_END
-        run_rows(m.msets, m.coef, cx, sm + m.off_M, dfc_lane);
     }
     if (JAC) {
         // the dq scratch is shared with part / vec / row (dead by now): restore its zero slot

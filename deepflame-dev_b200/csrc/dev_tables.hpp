@@ -97,7 +97,11 @@ struct DevMech {
     // third-body efficiency sets: M_s = dflt_s*Ctot + sum_j (eff_sj - dflt_s) c_j
     // row programs
     const double* coef;    // distinct coefficients, coef[0] = 0
-    RowProg msets;         // c[N+2] -> M[n_msets]
+    // third-body sets, evaluated by the reaction's own lane: M_s = sum_t val_t * c[off_t] over the
+    // entries ms_rng[s] = first | count << 16; entry = {val (2 words), byte offset of c_j, 0};
+    // the default efficiency enters as the entry (dflt_s, slot N+1 = total concentration)
+    const U4* ms_ent;
+    const uint32_t* ms_rng;
     WdotProg wdot;         // q[R+1] -> part[n_part] -> w[NA]  (cold table: read once per launch)
     RowProg jac;           // dq[n_dq+1] -> J[(NA+1)*ldj]; column NA holds gsum_i = sum_r nu_ir dflt_r dq_r/d[M]
 };

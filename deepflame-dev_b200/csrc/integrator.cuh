@@ -423,7 +423,6 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
                 const int row = tl + kTeam * s;
                 if (row < NA) {
                     const double inc = stage_point<NSLOT>(5, DFC_LR.k, s, DFC_LR.k[kStages - 1][s]);
-                    DFC_LR.inc[s] = inc;
                     const double cn = c[row] + inc;
                     const double sc = atol_rho / DFC_LDG(m.W + row) + rtol * fmax(fabs(c[row]), fabs(cn));
                     const double e = DFC_LR.k[kStages - 1][s] / sc;
@@ -446,8 +445,11 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
                 for (int s = 0; s < NSLOT; ++s) {
                     const int row = tl + kTeam * s;
                     if (row < NA) {
-                        DFC_LR.dc[s] += DFC_LR.inc[s];
-                        c[row] = DFC_LR.c0[s] + DFC_LR.dc[s];
+                        // the increment is recomputed (five FMAs) rather than kept live across the test;
+                        // dc carries c(t) - c(0) for RR, c itself only feeds the rate evaluation
+                        const double inc = stage_point<NSLOT>(5, DFC_LR.k, s, DFC_LR.k[kStages - 1][s]);
+                        DFC_LR.dc[s] += inc;
+                        c[row] += inc;
                     }
                 }
                 DFC_LANES_END

@@ -1,4 +1,4 @@
-# GPU-box routine: parity tests, full bench, launch list + one full ncu capture of the solve kernel
+# GPU-box routine: parity tests, full bench, launch list + full ncu captures of the solve and thermo kernels
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
 python bench.py ${BENCH_ARGS:-} > gpurun_out/bench_full.json 2> gpurun_out/bench_full.err
@@ -6,5 +6,7 @@ B="python bench.py --cells 131072 --steps 1 --warmup 1 --no-cpu-baseline"
 if [ -z "$SKIP_NCU" ]; then
 $B > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches.csv $B > gpurun_out/ncu1.log 2>&1
 $B > gpurun_out/plain2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:solve_kernel -c 1 -o gpurun_out/prof_solve $B > gpurun_out/ncu2.log 2>&1
+BT="python bench.py --cells 4194304 --steps 1 --warmup 1 --no-cpu-baseline --thermo-only"
+$BT > gpurun_out/plain3.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:thermo_kernel -s 6 -c 2 -o gpurun_out/prof_thermo $BT > gpurun_out/ncu3.log 2>&1
 fi
 tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/bench_full.json

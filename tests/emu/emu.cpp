@@ -89,7 +89,7 @@ void emu_destroy(void* h) { delete static_cast<Emu*>(h); }
 void emu_info(void* h, int* out) {
     const DevMech& m = static_cast<Emu*>(h)->dm;
     int v[] = {m.N, m.NA, m.NP, m.R, m.n_msets, m.n_fall, m.n_pow, m.n_dq, m.n_part, m.cell_doubles,
-               m.wdot.nA, m.msets.nA + m.msets.nB, m.jac.nA + m.jac.nB, static_cast<Emu*>(h)->ht.jac_entries,
+               m.wdot.nA, 0, m.jac.nA + m.jac.nB, static_cast<Emu*>(h)->ht.jac_entries,
                static_cast<Emu*>(h)->ht.wdot_entries};
     std::memcpy(out, v, sizeof(v));
 }
