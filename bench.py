@@ -136,7 +136,7 @@ def run_reference(args, rank):
 
     m = OM.deserialize(synth.load_blob(args.mech))
     threads = os.cpu_count() or 1
-    sample = args.ref_cells or 64 * threads
+    sample = args.ref_cells or 2048 * threads     # ~6 s of CPU work per step on 16 cores
     batch = synth.make_batch(args.mech, m.species, m.W, sample, seed=12345)
     times = []
     for i in range(args.warmup + args.steps):
@@ -190,6 +190,12 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank)
         return
+
+    # stdout carries exactly one JSON line: anything libraries print there meanwhile (NCCL's version
+    # banner, ...) is sent to stderr instead
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
 
     import torch
     import torch.distributed as dist
@@ -302,6 +308,8 @@ def main():
 
     if args.thermo_only:
         th = thermo_leg()
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
         if rank == 0:
             print(json.dumps({"thermo": th, "n_gpus": world, "cells_per_gpu": n}), flush=True)
         if world > 1:
@@ -400,6 +408,8 @@ def main():
             out["cpu_baseline"] = {"value": r1, "unit": UNIT, "cores": threads, "kind": "port",
                                    "sample": f"first {sample} cells of the same batch, {el1:.1f} s, "
                                              f"{bsteps:.1f} BDF steps/cell (oracle/c: CVODE-equivalent BDF + FD Jacobian + dense LU)"}
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()

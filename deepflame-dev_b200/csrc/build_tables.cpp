@@ -71,6 +71,8 @@ TargetRows make_rows(const GTarget& t, CoefTable& ct, int zero_src) {
 
 // Whole targets onto kTeam lanes, longest first onto the least loaded lane (a type-B row costs
 // about 1.75 type-A rows).  All rows of a target stay on one lane: first row stores, rest add.
+// Idle rows (lanes with fewer rows than the longest) write their zero sum to dump slot
+// dst_limit + lane, so the interpreter needs no "skip" test.
 HostRowProg pack_rows(std::vector<TargetRows> targets, int dst_limit) {
     auto cost = [](const TargetRows& t) { return 4 * (int)t.a.size() + 7 * (int)t.b.size(); };
     std::stable_sort(targets.begin(), targets.end(),
@@ -108,8 +110,9 @@ HostRowProg pack_rows(std::vector<TargetRows> targets, int dst_limit) {
     }
     const int n = p.nA + p.nB;
     p.ent.assign((size_t)std::max(n, 1) * kTeam, U4{0, 0, 0, 0});
-    p.dst.assign((size_t)std::max(n, 1) * kTeam, kRowSkip);
+    p.dst.assign((size_t)std::max(n, 1) * kTeam, 0u);
     for (int l = 0; l < kTeam; ++l) {
+        for (int i = 0; i < std::max(n, 1); ++i) p.dst[(size_t)i * kTeam + l] = (uint32_t)(dst_limit + l) * 8u;
         for (size_t i = 0; i < lane[l].a.size(); ++i) {
             p.ent[i * kTeam + l] = lane[l].a[i];
             p.dst[i * kTeam + l] = lane[l].da[i];
@@ -416,7 +419,7 @@ HostTables build_tables(const Mechanism& m) {
         L.off_vec = o; o += (NP + 1) & ~1;
         L.off_row = o;
     }
-    L.off_J = take((NA + 1) * ldj);
+    L.off_J = take((NA + 1) * ldj + kTeam);  // + dump slots of the Jacobian row program
     L.off_red = take(kTeam);  // dump slots of the wdot schedule
     L.cell_doubles = off;
 

@@ -120,6 +120,7 @@ struct LaneRegs {
     double k[kStages][NSLOT]; // stage increments
     double dc[NSLOT];         // accumulated increment c(t) - c(0) (kept separately: RR needs c - c0)
     double f0[NSLOT];         // wdot at the step's base point
+    double atolc[NSLOT];      // atol * rho / W_row: the absolute part of the error weights
     double red;               // this lane's term of a team reduction (team_sum)
     // this lane's rows of the wdot schedule: byte offsets of s0..s3 and dst (load_wdot_regs)
     static constexpr int RW = wdot_rows_cap(NP);
@@ -330,11 +331,9 @@ DFC_HD void run_rows(const RowProg& g, const double* coef, const double* src, do
         const double v2 = signed_by(ldb(src, u.z & 0xFFFFu), u.z);
         const double v3 = signed_by(ldb(src, u.w & 0xFFFFu), u.w);
         double sum = (v0 + v1) + (v2 + v3);
-        if (d != kRowSkip) {
-            double* out = ptrb(dst, d & 0xFFFFFFu);
-            if (d & kRowAcc) sum += *out;
-            *out = sum;
-        }
+        double* out = ptrb(dst, d & 0xFFFFFFu);
+        if (d & kRowAcc) sum += *out;
+        *out = sum;
     }
     DFC_NOUNROLL
     for (int i = 0; i < g.nB; ++i, e += kTeam, dp += kTeam) {
@@ -345,11 +344,9 @@ DFC_HD void run_rows(const RowProg& g, const double* coef, const double* src, do
         s0 = fma(coef[(u.z >> 16) & 0x7Fu], ldb(src, u.z & 0xFFFFu), s0);
         s1 = fma(coef[(u.w >> 16) & 0x7Fu], ldb(src, u.w & 0xFFFFu), s1);
         double sum = s0 + s1;
-        if (d != kRowSkip) {
-            double* out = ptrb(dst, d & 0xFFFFFFu);
-            if (d & kRowAcc) sum += *out;
-            *out = sum;
-        }
+        double* out = ptrb(dst, d & 0xFFFFFFu);
+        if (d & kRowAcc) sum += *out;
+        *out = sum;
     }
     DFC_LANES_END
 }

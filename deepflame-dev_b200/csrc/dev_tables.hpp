@@ -32,9 +32,9 @@ struct alignas(16) U4 {
 //   type-B rows (i >= nA): value = coef[id] * src    entry = src_byte_offset | id << 16
 // Integer stoichiometric coefficients are expanded into repeated +/-1 entries, so the common case
 // needs no coefficient load and no multiply.  Padding entries point at a slot that holds 0.0
-// (type A) or use coef[0] = 0 (type B).  dst == kRowSkip marks a padding row.  Rows that share a
+// (type A) or use coef[0] = 0 (type B); idle rows write 0 to a per-lane dump slot.  Rows that share a
 // destination are scheduled on the same lane in program order, so `accumulate` needs no atomics.
-constexpr uint32_t kRowSkip = 0xFFFFFFFFu, kRowAcc = 0x80000000u;
+constexpr uint32_t kRowAcc = 0x80000000u;
 struct RowProg {
     int nA, nB;
     const U4* ent;

