@@ -364,7 +364,7 @@ int dfchem_correct_thermo_dev(dfchem_handle h, int n, const double* he, const do
     if (n == 0) return DFCHEM_OK;
     CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    const int grid = (n + 255) / 256, N = h->mech.N;
+    const int N = h->mech.N, grid = std::min((n + 255) / 256, h->sm_count * 8);
     const size_t tsm = thermo_smem_bytes(N);
     if (tsm > 48 * 1024) return fail(h, DFCHEM_EUNSUPPORTED, "thermo kernel: species tables exceed 48 KB of shared memory");
     thermo_kernel<<<grid, 256, tsm, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
@@ -409,7 +409,7 @@ int dfchem_h_from_T_dev(dfchem_handle h, int n, const double* T, const double* Y
     if (n < 0 || (n > 0 && (!T || !Y || !he)) || ldY < n) return fail(h, DFCHEM_EINVAL, "dfchem_h_from_T_dev: bad argument");
     if (n == 0) return DFCHEM_OK;
     CUDA_TRY(h, cudaSetDevice(h->device));
-    enthalpy_kernel<<<(n + 255) / 256, 256, thermo_smem_bytes(h->mech.N), static_cast<cudaStream_t>(stream)>>>(
+    enthalpy_kernel<<<std::min((n + 255) / 256, h->sm_count * 8), 256, thermo_smem_bytes(h->mech.N), static_cast<cudaStream_t>(stream)>>>(
         h->dm, n, T, Y, ldY, he);
     CUDA_TRY(h, cudaGetLastError());
     return DFCHEM_OK;

@@ -95,7 +95,7 @@ wdot_kernel(const DevMech mg, int nC, const double* T, const double* p, const do
 // species' T_mid.  Nothing composition-sized is kept in registers, so occupancy is high.
 // Tables in shared memory: per species 16 doubles [range][a0..a6, 0] (range offset 64 B), then
 // 1/W, T_mid and the caller's species index.
-constexpr int kThermoBatch = 12;
+constexpr int kThermoBatch = 18;
 struct ThermoSmem {
     const double* nasa;   // [N][2][8]
     const double* rW;     // [N]
@@ -142,80 +142,81 @@ thermo_kernel(const DevMech m, int n, const double* __restrict__ he, const doubl
               double* __restrict__ rho, double* __restrict__ cp_out, double* __restrict__ hai, int ldH) {
     extern __shared__ double2 dfc_smem[];
     const ThermoSmem t = stage_thermo_tables(m, reinterpret_cast<double*>(dfc_smem));
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= n) return;
     const int N = m.N;
-    const double htarget = he[c];
-    const double* __restrict__ Yc = Y + c;
-    double Tc = T[c];
-    double Tsel = Tc;  // temperature the NASA ranges are selected at
-    double rw = 0.0, cp = 0.0;
-    for (int pass = 0; pass < 4; ++pass) {
-        double ysum = 0.0, B0 = 0.0, B1 = 0.0, B2 = 0.0, B3 = 0.0, B4 = 0.0, B5 = 0.0;
-        rw = 0.0;
-        // batches of kThermoBatch species: all loads of a batch are issued before its arithmetic, so
-        // that each thread keeps that many 8-byte HBM requests in flight
-        auto accumulate = [&](int k, double y) {
-            const double2* a = reinterpret_cast<const double2*>(t.nasa + (size_t)k * 16 + (Tsel <= t.Tmid[k] ? 0 : 8));
-            const double w = y * t.rW[k];
-            const double2 a01 = a[0], a23 = a[1], a45 = a[2];
-            ysum += y;
-            rw += w;
-            B0 = fma(w, a01.x, B0);
-            B1 = fma(w, a01.y, B1);
-            B2 = fma(w, a23.x, B2);
-            B3 = fma(w, a23.y, B3);
-            B4 = fma(w, a45.x, B4);
-            B5 = fma(w, a45.y, B5);
-        };
-        int k0 = 0;
-        for (; k0 + kThermoBatch <= N; k0 += kThermoBatch) {
-            double yv[kThermoBatch];
-#pragma unroll
-            for (int u = 0; u < kThermoBatch; ++u) yv[u] = Yc[(size_t)t.perm[k0 + u] * ldY];
-#pragma unroll
-            for (int u = 0; u < kThermoBatch; ++u) accumulate(k0 + u, yv[u]);
-        }
-        for (; k0 < N; ++k0) accumulate(k0, Yc[(size_t)t.perm[k0] * ldY]);
-        // Y is normalised by its sum (setState_PY); fold R in as well
-        const double sc = kGasConstant / ysum;
-        rw /= ysum;
-        B0 *= sc; B1 *= sc; B2 *= sc; B3 *= sc; B4 *= sc; B5 *= sc;
-        const double H1 = B1 * 0.5, H2 = B2 * (1.0 / 3.0), H3 = B3 * 0.25, H4 = B4 * 0.2;
-        for (int it = 0; it < 60; ++it) {
-            const double h = B5 + Tc * (B0 + Tc * (H1 + Tc * (H2 + Tc * (H3 + Tc * H4))));
+    // persistent CTAs (grid = a few per SM): the tables are staged once per CTA, cells in a grid-stride loop
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
+        const double htarget = he[c];
+        const double* __restrict__ Yc = Y + c;
+        double Tc = T[c];
+        double Tsel = Tc;  // temperature the NASA ranges are selected at
+        double rw = 0.0, cp = 0.0;
+        for (int pass = 0; pass < 4; ++pass) {
+            double ysum = 0.0, B0 = 0.0, B1 = 0.0, B2 = 0.0, B3 = 0.0, B4 = 0.0, B5 = 0.0;
+            rw = 0.0;
+            // batches of kThermoBatch species: all loads of a batch are issued before its arithmetic, so
+            // that each thread keeps that many 8-byte HBM requests in flight
+            auto accumulate = [&](int k, double y) {
+                const double2* a = reinterpret_cast<const double2*>(t.nasa + (size_t)k * 16 + (Tsel <= t.Tmid[k] ? 0 : 8));
+                const double w = y * t.rW[k];
+                const double2 a01 = a[0], a23 = a[1], a45 = a[2];
+                ysum += y;
+                rw += w;
+                B0 = fma(w, a01.x, B0);
+                B1 = fma(w, a01.y, B1);
+                B2 = fma(w, a23.x, B2);
+                B3 = fma(w, a23.y, B3);
+                B4 = fma(w, a45.x, B4);
+                B5 = fma(w, a45.y, B5);
+            };
+            int k0 = 0;
+            for (; k0 + kThermoBatch <= N; k0 += kThermoBatch) {
+                double yv[kThermoBatch];
+    #pragma unroll
+                for (int u = 0; u < kThermoBatch; ++u) yv[u] = Yc[(size_t)t.perm[k0 + u] * ldY];
+    #pragma unroll
+                for (int u = 0; u < kThermoBatch; ++u) accumulate(k0 + u, yv[u]);
+            }
+            for (; k0 < N; ++k0) accumulate(k0, Yc[(size_t)t.perm[k0] * ldY]);
+            // Y is normalised by its sum (setState_PY); fold R in as well
+            const double sc = kGasConstant / ysum;
+            rw /= ysum;
+            B0 *= sc; B1 *= sc; B2 *= sc; B3 *= sc; B4 *= sc; B5 *= sc;
+            const double H1 = B1 * 0.5, H2 = B2 * (1.0 / 3.0), H3 = B3 * 0.25, H4 = B4 * 0.2;
+            for (int it = 0; it < 60; ++it) {
+                const double h = B5 + Tc * (B0 + Tc * (H1 + Tc * (H2 + Tc * (H3 + Tc * H4))));
+                cp = B0 + Tc * (B1 + Tc * (B2 + Tc * (B3 + Tc * B4)));
+                double dT = (h - htarget) / cp;
+                dT = fmax(-100.0, fmin(100.0, dT));
+                Tc -= dT;
+                if (fabs(dT) < 1e-10 * Tc) break;
+            }
             cp = B0 + Tc * (B1 + Tc * (B2 + Tc * (B3 + Tc * B4)));
-            double dT = (h - htarget) / cp;
-            dT = fmax(-100.0, fmin(100.0, dT));
-            Tc -= dT;
-            if (fabs(dT) < 1e-10 * Tc) break;
+            // every species must have been summed with the range that holds at the root; within
+            // 1e-9 T_mid of the switch point either range is taken as valid (the NASA fits are
+            // continuous there only to ~1e-4 K: a root that lands on T_mid by round-off must not jump)
+            bool consistent = true;
+            for (int j = 0; j < t.n_sw; ++j) {
+                const double tm = t.Tsw[j];
+                consistent = consistent && (((Tsel <= tm) == (Tc <= tm)) || fabs(Tc - tm) <= 1e-9 * tm);
+            }
+            if (consistent) break;
+            Tsel = Tc;
         }
-        cp = B0 + Tc * (B1 + Tc * (B2 + Tc * (B3 + Tc * B4)));
-        // every species must have been summed with the range that holds at the root; within
-        // 1e-9 T_mid of the switch point either range is taken as valid (the NASA fits are
-        // continuous there only to ~1e-4 K: a root that lands on T_mid by round-off must not jump)
-        bool consistent = true;
-        for (int j = 0; j < t.n_sw; ++j) {
-            const double tm = t.Tsw[j];
-            consistent = consistent && (((Tsel <= tm) == (Tc <= tm)) || fabs(Tc - tm) <= 1e-9 * tm);
-        }
-        if (consistent) break;
-        Tsel = Tc;
-    }
-    T[c] = Tc;
-    const double ps = 1.0 / (rw * kGasConstant * Tc);  // Wbar/(R T)
-    psi[c] = ps;
-    rho[c] = p[c] * ps;
-    if (cp_out) cp_out[c] = cp;
-    if (hai) {
-        const double RT = kGasConstant * Tc, rT = 1.0 / Tc;
-#pragma unroll 4
-        for (int k = 0; k < N; ++k) {
-            const double2* a = reinterpret_cast<const double2*>(t.nasa + (size_t)k * 16 + (Tc <= t.Tmid[k] ? 0 : 8));
-            const double2 a01 = a[0], a23 = a[1], a45 = a[2];
-            const double hrt = a01.x + Tc * (a01.y * 0.5 + Tc * (a23.x * (1.0 / 3.0) + Tc * (a23.y * 0.25 + Tc * (a45.x * 0.2)))) +
-                               a45.y * rT;
-            hai[(size_t)t.perm[k] * ldH + c] = hrt * RT * t.rW[k];
+        T[c] = Tc;
+        const double ps = 1.0 / (rw * kGasConstant * Tc);  // Wbar/(R T)
+        psi[c] = ps;
+        rho[c] = p[c] * ps;
+        if (cp_out) cp_out[c] = cp;
+        if (hai) {
+            const double RT = kGasConstant * Tc, rT = 1.0 / Tc;
+    #pragma unroll 4
+            for (int k = 0; k < N; ++k) {
+                const double2* a = reinterpret_cast<const double2*>(t.nasa + (size_t)k * 16 + (Tc <= t.Tmid[k] ? 0 : 8));
+                const double2 a01 = a[0], a23 = a[1], a45 = a[2];
+                const double hrt = a01.x + Tc * (a01.y * 0.5 + Tc * (a23.x * (1.0 / 3.0) + Tc * (a23.y * 0.25 + Tc * (a45.x * 0.2)))) +
+                                   a45.y * rT;
+                hai[(size_t)t.perm[k] * ldH + c] = hrt * RT * t.rW[k];
+            }
         }
     }
 }
@@ -243,21 +244,21 @@ enthalpy_kernel(const DevMech m, int n, const double* __restrict__ T, const doub
                 int ldY, double* __restrict__ he) {
     extern __shared__ double2 dfc_smem[];
     const ThermoSmem t = stage_thermo_tables(m, reinterpret_cast<double*>(dfc_smem));
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= n) return;
-    const double Tc = T[c], rT = 1.0 / Tc;
-    double ysum = 0.0, h = 0.0;
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
+        const double Tc = T[c], rT = 1.0 / Tc;
+        double ysum = 0.0, h = 0.0;
 #pragma unroll 4
-    for (int k = 0; k < m.N; ++k) {
-        const double y = Y[(size_t)t.perm[k] * ldY + c];
-        const double2* a = reinterpret_cast<const double2*>(t.nasa + (size_t)k * 16 + (Tc <= t.Tmid[k] ? 0 : 8));
-        const double2 a01 = a[0], a23 = a[1], a45 = a[2];
-        const double hrt = a01.x + Tc * (a01.y * 0.5 + Tc * (a23.x * (1.0 / 3.0) + Tc * (a23.y * 0.25 + Tc * (a45.x * 0.2)))) +
-                           a45.y * rT;
-        ysum += y;
-        h = fma(y * t.rW[k], hrt, h);
+        for (int k = 0; k < m.N; ++k) {
+            const double y = Y[(size_t)t.perm[k] * ldY + c];
+            const double2* a = reinterpret_cast<const double2*>(t.nasa + (size_t)k * 16 + (Tc <= t.Tmid[k] ? 0 : 8));
+            const double2 a01 = a[0], a23 = a[1], a45 = a[2];
+            const double hrt = a01.x + Tc * (a01.y * 0.5 + Tc * (a23.x * (1.0 / 3.0) + Tc * (a23.y * 0.25 + Tc * (a45.x * 0.2)))) +
+                               a45.y * rT;
+            ysum += y;
+            h = fma(y * t.rW[k], hrt, h);
+        }
+        he[c] = h * kGasConstant * Tc / ysum;
     }
-    he[c] = h * kGasConstant * Tc / ysum;
 }
 
 }  // namespace dfchem
