@@ -80,7 +80,7 @@ cudaError_t configure_t(dfchem_ctx* h) {
     if (e != cudaSuccess) return e;
     // persistent CTA, one per SM: as many warps (cells in flight) as shared memory allows
     const size_t cell = (size_t)h->dm.cell_doubles * sizeof(double);
-    h->warps = (int)std::min<size_t>(kMaxWarps, ((size_t)max_optin - h->dm.hot_bytes) / cell);
+    h->warps = (int)std::min<size_t>(max_warps(NP), ((size_t)max_optin - h->dm.hot_bytes) / cell);
     if (h->warps < 1) return cudaErrorLaunchOutOfResources;
     // the attribute is per kernel instantiation and shared by every handle using it: always the
     // device maximum, never this handle's size

@@ -9,7 +9,10 @@ namespace dfchem {
 
 // Shared memory of a CTA: [hot tables (m.hot_bytes)] [one cell block per warp (m.cell_doubles)].
 // The CTA is persistent (one per SM); its warps are independent after the table staging.
-constexpr int kMaxWarps = 8;
+// Warps (= cells in flight) per CTA by kernel size class: mechanisms with up to 24 active species need
+// few enough registers (<= 128 per thread) for 16 warps; the larger ones are capped at 8 by their
+// register-resident matrix rows and schedules (and by shared memory).
+constexpr int max_warps(int NP) { return NP <= 24 ? 16 : 8; }
 
 __device__ __forceinline__ DevMech stage_hot_tables(const DevMech& m, unsigned char* smem) {
     const uint4* src = reinterpret_cast<const uint4*>(m.hot_base);
@@ -21,7 +24,7 @@ __device__ __forceinline__ DevMech stage_hot_tables(const DevMech& m, unsigned c
 
 // counters[0] accepted steps, [1] rejected steps, [2] failed cells
 template <int NP, int NSLOT>
-__global__ void __launch_bounds__(kMaxWarps* kTeam, 1)
+__global__ void __launch_bounds__(max_warps(NP) * kTeam, 1)
 solve_kernel(const DevMech mg, const SolveArgs a, unsigned int* queue, unsigned long long* counters) {
     extern __shared__ double2 dfc_smem[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(dfc_smem);
@@ -61,7 +64,7 @@ solve_kernel(const DevMech mg, const SolveArgs a, unsigned int* queue, unsigned 
 }
 
 template <int NP, int NSLOT>
-__global__ void __launch_bounds__(kMaxWarps* kTeam, 1)
+__global__ void __launch_bounds__(max_warps(NP) * kTeam, 1)
 wdot_kernel(const DevMech mg, int nC, const double* T, const double* p, const double* Y, int ldY,
             double* wr, int ldW, unsigned int* queue) {
     extern __shared__ double2 dfc_smem[];
@@ -95,7 +98,7 @@ wdot_kernel(const DevMech mg, int nC, const double* T, const double* p, const do
 // species' T_mid.  Nothing composition-sized is kept in registers, so occupancy is high.
 // Tables in shared memory: per species 16 doubles [range][a0..a6, 0] (range offset 64 B), then
 // 1/W, T_mid and the caller's species index.
-constexpr int kThermoBatch = 18;
+constexpr int kThermoBatch = 12;
 struct ThermoSmem {
     const double* nasa;   // [N][2][8]
     const double* rW;     // [N]

@@ -17,7 +17,7 @@ from ctypes import POINTER, c_char_p, c_double, c_int, c_size_t, c_ulonglong, c_
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libdfchem_b200.so")
+LIB_PATH = os.environ.get("DFCHEM_LIB") or os.path.join(os.path.dirname(_HERE), "libdfchem_b200.so")  # DFCHEM_LIB: experiment builds
 GREAT = 1.0e15  # OpenFOAM's `great` (double precision), returned by updateReactionRates (.C:871,894)
 
 _dp = POINTER(c_double)
