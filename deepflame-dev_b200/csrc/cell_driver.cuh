@@ -26,6 +26,15 @@ struct SolveArgs {
 };
 
 // set up c (all N species), cs (inert tail), regs.c0/dc; returns rho_ct; ysum via reference
+// once per team, before its first cell: Jacobian entries that no reaction touches are never
+// written afterwards and stay zero for the whole launch
+DFC_HD void clear_jacobian(const DevMech& m, double* sm, int dfc_lane) {
+    (void)dfc_lane;
+    DFC_LANES_BEGIN
+    for (int i = tl; i < (m.NA + 1) * m.ldj; i += kTeam) sm[m.off_J + i] = 0.0;
+    DFC_LANES_END
+}
+
 template <int NP, int NSLOT>
 DFC_HD double load_cell_state(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* regs, int dfc_lane,
                               const double* Y, int ldY, int cell, double T, double p, double& ysum) {

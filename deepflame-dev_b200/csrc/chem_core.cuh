@@ -179,11 +179,32 @@ DFC_HD DevMech rebase_hot(const DevMech& m, const uint8_t* nb) {
     return r;
 }
 
+// Host emulation only (tests/emu, -DDFC_EMU_BOUNDS): every table-driven address is checked
+// against the cell block the emulator registered; on the device the macro is empty.
+#if !defined(__CUDA_ARCH__) && defined(DFC_EMU_BOUNDS)
+struct EmuWindow {
+    const char* lo;
+    const char* hi;
+    void (*fail)(const void*);
+};
+extern thread_local EmuWindow dfc_emu_window;
+inline void dfc_check_addr(const void* p) {
+    const char* q = static_cast<const char*>(p);
+    if (dfc_emu_window.lo && (q < dfc_emu_window.lo || q + sizeof(double) > dfc_emu_window.hi))
+        dfc_emu_window.fail(p);
+}
+#define DFC_CHECK_ADDR(p) dfc_check_addr(p)
+#else
+#define DFC_CHECK_ADDR(p) ((void)0)
+#endif
+
 // byte-offset addressing of the per-cell arrays (offsets come pre-scaled from the tables)
 DFC_HD double ldb(const double* base, uint32_t byte_off) {
+    DFC_CHECK_ADDR(reinterpret_cast<const char*>(base) + byte_off);
     return *reinterpret_cast<const double*>(reinterpret_cast<const char*>(base) + byte_off);
 }
 DFC_HD double* ptrb(double* base, uint32_t byte_off) {
+    DFC_CHECK_ADDR(reinterpret_cast<char*>(base) + byte_off);
     return reinterpret_cast<double*>(reinterpret_cast<char*>(base) + byte_off);
 }
 DFC_HD U4 ld_u4(const U4* p) {
@@ -264,8 +285,14 @@ extern __shared__ double2 dfc_smem[];
 #else
 #define DFC_SMEM_BASE(sm) reinterpret_cast<char*>(sm)
 #endif
-DFC_HD double ldo(const char* base, uint32_t off) { return *reinterpret_cast<const double*>(base + off); }
-DFC_HD void sto(char* base, uint32_t off, double v) { *reinterpret_cast<double*>(base + off) = v; }
+DFC_HD double ldo(const char* base, uint32_t off) {
+    DFC_CHECK_ADDR(base + off);
+    return *reinterpret_cast<const double*>(base + off);
+}
+DFC_HD void sto(char* base, uint32_t off, double v) {
+    DFC_CHECK_ADDR(base + off);
+    *reinterpret_cast<double*>(base + off) = v;
+}
 
 // cell_off: byte offset of this team's cell block from DFC_SMEM_BASE (0 in the emulation)
 template <class Regs>

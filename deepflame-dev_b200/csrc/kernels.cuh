@@ -40,8 +40,7 @@ solve_kernel(const DevMech mg, const SolveArgs a, unsigned int* queue, unsigned 
     double* sm = reinterpret_cast<double*>(smem + cell_off);
     LaneRegs<NP, NSLOT> regs;
     load_wdot_regs(m, &regs, lane, cell_off);
-    // Jacobian entries that no reaction touches stay zero for the whole launch
-    for (int i = lane; i < (m.NA + 1) * m.ldj; i += kTeam) sm[m.off_J + i] = 0.0;
+    clear_jacobian(m, sm, lane);
     __syncwarp();
     unsigned long long acc = 0, rej = 0, bad = 0;
     while (true) {

@@ -3,16 +3,37 @@
 // with a "lane block" = for-loop over the 32 lanes, so the kernel logic and the mechanism
 // tables can be debugged and parity-checked against the oracle on a machine without a GPU.
 // It is never linked into libdfchem_b200.so; only tests/ build and call it.
+#include <cstdio>
 #include <cstring>
+#include <limits>
 #include <stdexcept>
+#include <string>
 #include <vector>
 
+#define DFC_EMU_BOUNDS 1
 #include "../../deepflame-dev_b200/csrc/cell_driver.cuh"
 #include "../../deepflame-dev_b200/csrc/dispatch.hpp"
 
 using namespace dfchem;
 
+// window of the cell block for the table-driven address checks (chem_core.cuh, DFC_CHECK_ADDR)
+namespace dfchem {
+thread_local EmuWindow dfc_emu_window = {nullptr, nullptr, nullptr};
+}
+
 namespace {
+void oob(const void* p) {
+    throw std::out_of_range("emulated cell block: table-driven address " +
+                            std::to_string(static_cast<const char*>(p) - dfc_emu_window.lo) + " outside [0, " +
+                            std::to_string(dfc_emu_window.hi - dfc_emu_window.lo) + ")");
+}
+struct Window {
+    explicit Window(const std::vector<double>& sm) {
+        dfc_emu_window = {reinterpret_cast<const char*>(sm.data()),
+                          reinterpret_cast<const char*>(sm.data() + sm.size()), &oob};
+    }
+    ~Window() { dfc_emu_window = {nullptr, nullptr, nullptr}; }
+};
 struct Emu {
     HostTables ht;
     DevMech dm;
@@ -20,10 +41,14 @@ struct Emu {
 template <int NP, int NSLOT>
 void solve_t(const DevMech& m, const SolveArgs& a, unsigned long long* counters) {
     std::vector<double> sm(m.cell_doubles, 0.0);
+    Window win(sm);
     std::vector<LaneRegs<NP, NSLOT>> regs(kTeam);
     if (!load_wdot_regs(m, regs.data(), 0, 0u)) throw std::runtime_error("wdot schedule too large");
     for (int cell = 0; cell < a.nC; ++cell) {
-        std::fill(sm.begin(), sm.end(), 0.0);
+        // the device never clears a cell block between cells: poison it, so that a read of a slot
+        // this cell has not written shows up as NaN in the results
+        std::fill(sm.begin(), sm.end(), std::numeric_limits<double>::quiet_NaN());
+        clear_jacobian(m, sm.data(), 0);
         StepStats st;
         solve_one_cell<NP, NSLOT>(m, a, sm.data(), regs.data(), 0, cell, st);
         counters[0] += st.accepted;
@@ -34,7 +59,8 @@ void solve_t(const DevMech& m, const SolveArgs& a, unsigned long long* counters)
 template <int NP, int NSLOT>
 void wdot_t(const DevMech& m, int nC, const double* T, const double* p, const double* Y, int ldY,
             double* wr, int ldW) {
-    std::vector<double> sm(m.cell_doubles, 0.0);
+    std::vector<double> sm(m.cell_doubles, std::numeric_limits<double>::quiet_NaN());
+    Window win(sm);
     std::vector<LaneRegs<NP, NSLOT>> regs(kTeam);
     if (!load_wdot_regs(m, regs.data(), 0, 0u)) throw std::runtime_error("wdot schedule too large");
     for (int cell = 0; cell < nC; ++cell)
@@ -44,10 +70,12 @@ void wdot_t(const DevMech& m, int nC, const double* T, const double* p, const do
 template <int NP, int NSLOT>
 void jac_t(const DevMech& m, double T, double p, const double* Y, double inv_hg, double* Jout,
            double* Ainv_out) {
-    std::vector<double> sm(m.cell_doubles, 0.0);
+    std::vector<double> sm(m.cell_doubles, std::numeric_limits<double>::quiet_NaN());
+    Window win(sm);
     std::vector<LaneRegs<NP, NSLOT>> regs(kTeam);
     if (!load_wdot_regs(m, regs.data(), 0, 0u)) throw std::runtime_error("wdot schedule too large");
     double ysum;
+    clear_jacobian(m, sm.data(), 0);
     load_cell_state<NP, NSLOT>(m, sm.data(), regs.data(), 0, Y, 1, 0, T, p, ysum);
     setup_rate_constants(m, sm.data(), T, 0);
     init_const_slots(m, sm.data(), 0);
@@ -86,6 +114,22 @@ void* emu_create(const void* blob, size_t len) {
     }
 }
 void emu_destroy(void* h) { delete static_cast<Emu*>(h); }
+// 1 when the address check fires for an offset one past a 4-double block (and not for the last one)
+int emu_bounds_selftest() {
+    std::vector<double> sm(4, 1.0);
+    Window win(sm);
+    try {
+        (void)ldb(sm.data(), 24u);
+    } catch (const std::exception&) {
+        return 0;
+    }
+    try {
+        (void)ldb(sm.data(), 32u);
+    } catch (const std::out_of_range&) {
+        return 1;
+    }
+    return 0;
+}
 void emu_info(void* h, int* out) {
     const DevMech& m = static_cast<Emu*>(h)->dm;
     int v[] = {m.N, m.NA, m.NP, m.R, m.n_msets, m.n_fall, m.n_pow, m.n_dq, m.n_part, m.cell_doubles,
@@ -105,7 +149,12 @@ int emu_solve(void* h, int nC, const double* T, const double* p, const double* r
     SolveArgs a{nC, T, p, rho, dt, dt_uniform, Y, ldY, RR, ldRR, Qdot, cost, status, rtol, atol, max_steps};
     counters[0] = counters[1] = counters[2] = 0;
 #define CALL(NP, NS) solve_t<NP, NS>(m, a, counters)
-    DFC_DISPATCH_NP(m.NP, CALL)
+    try {
+        DFC_DISPATCH_NP(m.NP, CALL)
+    } catch (const std::exception& e) {
+        std::fprintf(stderr, "emu: %s\n", e.what());
+        return -1;
+    }
 #undef CALL
     return 0;
 }
@@ -113,7 +162,12 @@ int emu_wdot(void* h, int nC, const double* T, const double* p, const double* Y,
              int ldW) {
     const DevMech& m = static_cast<Emu*>(h)->dm;
 #define CALL(NP, NS) wdot_t<NP, NS>(m, nC, T, p, Y, ldY, wr, ldW)
-    DFC_DISPATCH_NP(m.NP, CALL)
+    try {
+        DFC_DISPATCH_NP(m.NP, CALL)
+    } catch (const std::exception& e) {
+        std::fprintf(stderr, "emu: %s\n", e.what());
+        return -1;
+    }
 #undef CALL
     return 0;
 }
@@ -121,7 +175,12 @@ int emu_jacobian(void* h, double T, double p, const double* Y, double inv_hg, do
                  double* Ainv_out) {
     const DevMech& m = static_cast<Emu*>(h)->dm;
 #define CALL(NP, NS) jac_t<NP, NS>(m, T, p, Y, inv_hg, Jout, Ainv_out)
-    DFC_DISPATCH_NP(m.NP, CALL)
+    try {
+        DFC_DISPATCH_NP(m.NP, CALL)
+    } catch (const std::exception& e) {
+        std::fprintf(stderr, "emu: %s\n", e.what());
+        return -1;
+    }
 #undef CALL
     return 0;
 }

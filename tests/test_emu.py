@@ -45,11 +45,17 @@ def emu_solve(lib, h, g, rtol, atol, N):
     cnt = (ctypes.c_ulonglong * 4)()
     Y = np.ascontiguousarray(g["Y"])
     dt = np.ascontiguousarray(g["dt"])
-    lib.emu_solve(h, n, dp(np.ascontiguousarray(g["T"])), dp(np.ascontiguousarray(g["p"])),
+    rc = lib.emu_solve(h, n, dp(np.ascontiguousarray(g["T"])), dp(np.ascontiguousarray(g["p"])),
                   dp(np.ascontiguousarray(g["rho"])), dp(dt), ctypes.c_double(0.0), dp(Y), n, dp(RR), n, dp(Q),
                   dp(cost), st.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), ctypes.c_double(rtol),
                   ctypes.c_double(atol), 200000, cnt)
+    assert rc == 0          # -1: a table-driven address left the emulated cell block
     return RR, Q, cost, st
+
+
+def test_address_check_is_armed(emu):
+    """The emulator checks every table-driven address against the cell block (DFC_CHECK_ADDR)."""
+    assert emu.emu_bounds_selftest() == 1
 
 
 def test_table_shapes(emu):
@@ -72,8 +78,9 @@ def test_wdot_matches_golden(emu, name):
     h, info = create(emu, name)
     n = g["T"].shape[0]
     wr = np.zeros((info["N"], n))
-    emu.emu_wdot(h, n, dp(np.ascontiguousarray(g["T"])), dp(np.ascontiguousarray(g["p"])),
+    rc = emu.emu_wdot(h, n, dp(np.ascontiguousarray(g["T"])), dp(np.ascontiguousarray(g["p"])),
                  dp(np.ascontiguousarray(g["Y"])), n, dp(wr), n)
+    assert rc == 0
     emu.emu_destroy(h)
     scale = np.abs(g["wrate"]).max(0, keepdims=True) + 1e-300
     assert (np.abs(wr - g["wrate"]) / scale).max() < 1e-12
@@ -96,8 +103,9 @@ def test_jacobian_and_inverse_match_oracle(emu, name):
         Jref = K.jacobian_C(m, K.RateConstants(m, T), C)[0]
         J, Ainv = np.zeros((N, N)), np.zeros((NA, NA))
         ihg = 1.0 / (2e-8 * 0.25)
-        emu.emu_jacobian(h, ctypes.c_double(T[0]), ctypes.c_double(p[0]), dp(np.ascontiguousarray(Yn)),
+        rc = emu.emu_jacobian(h, ctypes.c_double(T[0]), ctypes.c_double(p[0]), dp(np.ascontiguousarray(Yn)),
                          ctypes.c_double(ihg), dp(J), dp(Ainv))
+        assert rc == 0
         assert np.abs(J - Jref)[:, act].max() <= 1e-12 * np.abs(Jref).max()
         A = np.eye(NA) * ihg - Jref[np.ix_(act, act)]
         assert np.abs(Ainv @ A - np.eye(NA)).max() < 1e-9
