@@ -303,6 +303,34 @@ def main():
                 err = float((Tw - d["T"]).abs().max().item())
                 thermo[label] = {"cells_per_s": world * n / (ms_t * 1e-3), "ms": ms_t, "algorithmic_bytes_per_cell": nbytes,
                                  "achieved_GBps": nbytes * n / (ms_t * 1e-3) / 1e9, "max_abs_T_error_K": err}
+            # ---- transport part of correctThermo (FP64-bound: N^2 pair terms per cell) -------------
+            # gri30 has no thermo_<mech>.txt in the reference: synthetic fits of Cantera's functional form
+            visc, cond, diff = synth.synthetic_transport_fits(h.W)
+            h.set_transport_fits(visc, cond, diff)
+            mu, al = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(2))
+
+            def step_tr():
+                h.check(lib.dfchem_transport_dev(h.h, n, Tw.data_ptr(), d["p"].data_ptr(), rho2.data_ptr(), cpo.data_ptr(),
+                                                 d["Y"].data_ptr(), n, mu.data_ptr(), al.data_ptr(), hai.data_ptr(), n, 0,
+                                                 stream.cuda_stream))
+            for _ in range(2):
+                step_tr()
+            barrier()
+            t0e, t1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0e.record(stream)
+            for _ in range(3):
+                step_tr()
+            t1e.record(stream)
+            barrier()
+            ms_t = max_over_ranks(t0e.elapsed_time(t1e) / 3)
+            # per cell: N poly (4 fma) x2, Wilke N^2 x 5, diffusion N(N-1) x (4 fma poly + mul + rcp + 3), flops with fma = 2
+            flops = N * 2 * 9 + N * N * 9 + N * (N - 1) * 16 + 8 * N
+            thermo["mu_alpha_rhoD"] = {"cells_per_s": world * n / (ms_t * 1e-3), "ms": ms_t, "bound": "fp64",
+                                       "algorithmic_flops_per_cell": flops,
+                                       "achieved_TFLOPs": flops * n / (ms_t * 1e-3) / 1e12,
+                                       "algorithmic_bytes_per_cell": (N + 4) * 8 + (N + 2) * 8,
+                                       "fits": "synthetic (Cantera's ln T polynomial form)",
+                                       "finite": bool(torch.isfinite(mu).all().item() and torch.isfinite(hai).all().item())}
             del hai
         return thermo
 

@@ -519,6 +519,7 @@ HostTables build_tables(const Mechanism& m) {
     // ---- blob ------------------------------------------------------------------------------
     Blob B;
     ht.perm = perm;
+    ht.rorder = rorder;
     // hot prefix (staged in shared memory by the kernels)
     L.rdesc = as_ptr<U4>(B.add(rdesc));
     L.coef = as_ptr<double>(B.add(ct.v));

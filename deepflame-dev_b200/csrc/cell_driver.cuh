@@ -157,4 +157,22 @@ DFC_HD void wdot_one_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* reg
     DFC_LANES_END
 }
 
+// Net rates of progress q_r [kmol/m^3/s] at (T, p, Y) in the caller's reaction order: the
+// getNetRatesOfProgress call of calculateRR (dfChemistryModel.C:925-987), which projects one
+// reaction on one species as (nu''_i - nu'_i) q_r W_i.  rorder: internal -> caller's index.
+template <int NP, int NSLOT>
+DFC_HD void rop_one_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* regs, int dfc_lane,
+                         const double* T, const double* p, const double* Y, int ldY,
+                         const int* rorder, double* q_out, int ldQ, int cell) {
+    double ysum;
+    const double Tc = T[cell];
+    load_cell_state<NP, NSLOT>(m, sm, regs, dfc_lane, Y, ldY, cell, Tc, p[cell], ysum);
+    setup_rate_constants(m, sm, Tc, dfc_lane);
+    init_const_slots(m, sm, dfc_lane);
+    eval_wdot<false>(m, sm, sm + m.off_c, regs, dfc_lane);
+    DFC_LANES_BEGIN
+    for (int r = tl; r < m.R; r += kTeam) q_out[(size_t)DFC_LDG(rorder + r) * ldQ + cell] = sm[m.off_q + r];
+    DFC_LANES_END
+}
+
 }  // namespace dfchem

@@ -112,6 +112,7 @@ struct HostTables {
     DevMech layout{};            // pointer fields hold byte offsets into blob until rebase()
     std::vector<uint8_t> blob;
     std::vector<int> perm;       // internal -> caller
+    std::vector<int> rorder;     // internal reaction index -> index in the Mechanism record (caller's)
     int jac_entries = 0, wdot_entries = 0;
     DevMech rebase(const void* base) const;
 };

@@ -2,6 +2,7 @@
 // launch configuration, chunked H2D/compute/D2H pipeline for the host-pointer entry points.
 // There is deliberately no CPU path here: every entry point runs the sm_100a kernels or fails.
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -10,6 +11,7 @@
 #include "../../include/dfchem.h"
 #include "dispatch.hpp"
 #include "kernels.cuh"
+#include "transport.cuh"
 
 using namespace dfchem;
 
@@ -51,6 +53,9 @@ struct dfchem_ctx {
     unsigned int* d_queue = nullptr;          // kSlots + 1 counters (last: dev API)
     unsigned long long* d_counters = nullptr; // 3
     unsigned long long launches = 0;
+    int* d_rorder = nullptr;                  // [R] internal -> caller's reaction index (rop kernel)
+    DevBuf d_transport;                       // transport fit tables (dfchem_set_transport_fits)
+    TransportTab tt{};
     std::string err;
 };
 
@@ -89,6 +94,8 @@ cudaError_t configure_t(dfchem_ctx* h) {
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(wdot_kernel<NP, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin);
     if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(rop_kernel<NP, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin);
+    if (e != cudaSuccess) return e;
     int nb = 0;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, solve_kernel<NP, NSLOT>, h->warps * kTeam, smem);
     if (e != cudaSuccess) return e;
@@ -105,6 +112,13 @@ void launch_wdot_t(dfchem_ctx* h, int nC, const double* T, const double* p, cons
                    double* wr, int ldW, unsigned int* queue, cudaStream_t s) {
     const int grid = std::max(1, std::min(h->sm_count, (nC + h->warps - 1) / h->warps));
     wdot_kernel<NP, NSLOT><<<grid, h->warps * kTeam, smem_bytes(h), s>>>(h->dm, nC, T, p, Y, ldY, wr, ldW, queue);
+}
+
+template <int NP, int NSLOT>
+void launch_rop_t(dfchem_ctx* h, int nC, const double* T, const double* p, const double* Y, int ldY,
+                  double* q, int ldQ, unsigned int* queue, cudaStream_t s) {
+    const int grid = std::max(1, std::min(h->sm_count, (nC + h->warps - 1) / h->warps));
+    rop_kernel<NP, NSLOT><<<grid, h->warps * kTeam, smem_bytes(h), s>>>(h->dm, nC, T, p, Y, ldY, h->d_rorder, q, ldQ, queue);
 }
 
 int launch_solve(dfchem_ctx* h, const SolveArgs& a, int qslot, cudaStream_t s) {
@@ -153,6 +167,11 @@ int finish_create(dfchem_ctx* h, int device, dfchem_handle* out) {
     if ((e = cudaMalloc(&h->d_queue, (kSlots + 1) * sizeof(unsigned int))) != cudaSuccess) return bail("cudaMalloc", e);
     if ((e = cudaMalloc(&h->d_counters, 3 * sizeof(unsigned long long))) != cudaSuccess) return bail("cudaMalloc", e);
     cudaMemset(h->d_counters, 0, 3 * sizeof(unsigned long long));
+    if (h->mech.R > 0) {
+        if ((e = cudaMalloc(&h->d_rorder, h->mech.R * sizeof(int))) != cudaSuccess) return bail("cudaMalloc", e);
+        if ((e = cudaMemcpy(h->d_rorder, h->ht.rorder.data(), h->mech.R * sizeof(int), cudaMemcpyHostToDevice)) != cudaSuccess)
+            return bail("cudaMemcpy(rorder)", e);
+    }
     for (int i = 0; i < kSlots; ++i)
         if ((e = cudaStreamCreateWithFlags(&h->streams[i], cudaStreamNonBlocking)) != cudaSuccess)
             return bail("cudaStreamCreate", e);
@@ -213,6 +232,8 @@ void dfchem_destroy(dfchem_handle h) {
     if (h->d_blob) cudaFree(h->d_blob);
     if (h->d_queue) cudaFree(h->d_queue);
     if (h->d_counters) cudaFree(h->d_counters);
+    if (h->d_rorder) cudaFree(h->d_rorder);
+    h->d_transport.release();
     delete h;
 }
 
@@ -430,6 +451,169 @@ int dfchem_h_from_T(dfchem_handle h, int n, const double* T, const double* Y, in
     int rc = dfchem_h_from_T_dev(h, n, d, d + 2 * ld, n, d + ld, s);
     if (rc != DFCHEM_OK) return rc;
     CUDA_TRY(h, cudaMemcpyAsync(he, d + ld, nb, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(h, cudaStreamSynchronize(s));
+    return DFCHEM_OK;
+}
+
+// ---- rates of progress (calculateRR, dfChemistryModel.C:925-987) --------------------------------
+int dfchem_rop_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* Y, int ldY,
+                   double* q, int ldQ, void* stream) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC < 0 || (nC > 0 && (!T || !p || !Y || !q)) || ldY < nC || ldQ < nC)
+        return fail(h, DFCHEM_EINVAL, "dfchem_rop_dev: bad argument");
+    if (nC == 0 || h->mech.R == 0) return DFCHEM_OK;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    unsigned int* queue = h->d_queue + kSlots;
+    CUDA_TRY(h, cudaMemsetAsync(queue, 0, sizeof(unsigned int), s));
+#define CALL(NP, NS) launch_rop_t<NP, NS>(h, nC, T, p, Y, ldY, q, ldQ, queue, s)
+    DFC_DISPATCH_NP(h->dm.NP, CALL)
+#undef CALL
+    CUDA_TRY(h, cudaGetLastError());
+    return DFCHEM_OK;
+}
+
+int dfchem_rop(dfchem_handle h, int nC, const double* T, const double* p, const double* Y, int ldY,
+               double* q, int ldQ) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC < 0 || (nC > 0 && (!T || !p || !Y || !q)) || ldY < nC || ldQ < nC)
+        return fail(h, DFCHEM_EINVAL, "dfchem_rop: bad argument");
+    if (nC == 0 || h->mech.R == 0) return DFCHEM_OK;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    const int N = h->mech.N, R = h->mech.R;
+    const size_t ld = (size_t)nC, nb = ld * sizeof(double);
+    CUDA_TRY(h, h->scratch.ensure(((size_t)N + R + 2) * nb));
+    double* d = static_cast<double*>(h->scratch.p);
+    double *dT = d, *dp = d + ld, *dY = d + 2 * ld, *dQ = dY + (size_t)N * ld;
+    cudaStream_t s = h->streams[0];
+    CUDA_TRY(h, cudaMemcpyAsync(dT, T, nb, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(h, cudaMemcpyAsync(dp, p, nb, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(h, cudaMemcpy2DAsync(dY, nb, Y, (size_t)ldY * sizeof(double), nb, N, cudaMemcpyHostToDevice, s));
+    int rc = dfchem_rop_dev(h, nC, dT, dp, dY, nC, dQ, nC, s);
+    if (rc != DFCHEM_OK) return rc;
+    CUDA_TRY(h, cudaMemcpy2DAsync(q, (size_t)ldQ * sizeof(double), dQ, nb, nb, R, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(h, cudaStreamSynchronize(s));
+    return DFCHEM_OK;
+}
+
+int dfchem_reaction_stoich(dfchem_handle h, int reaction, double* nu_net) {
+    if (!h || !nu_net || reaction < 0 || reaction >= h->mech.R) return fail(h, DFCHEM_EINVAL, "dfchem_reaction_stoich: bad argument");
+    const Mechanism& m = h->mech;
+    std::fill(nu_net, nu_net + m.N, 0.0);
+    for (int a = 0; a < kMaxSide; ++a) {
+        const int ri = m.r_idx[reaction * kMaxSide + a], pi = m.p_idx[reaction * kMaxSide + a];
+        if (ri >= 0) nu_net[ri] -= m.r_nu[reaction * kMaxSide + a];
+        if (pi >= 0) nu_net[pi] += m.p_nu[reaction * kMaxSide + a];
+    }
+    return DFCHEM_OK;
+}
+
+// ---- transport (correctThermo mu / alpha / rhoD, dfChemistryModel.C:513-541) -----------------------
+int dfchem_set_transport_fits(dfchem_handle h, const double* visc, const double* cond, const double* diff) {
+    if (!h || !visc || !cond || !diff) return fail(h, DFCHEM_EINVAL, "dfchem_set_transport_fits: bad argument");
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    const int N = h->mech.N;
+    const std::vector<double>& W = h->mech.W;
+    const size_t nW = (size_t)N, nV = (size_t)N * kDiffStride, nK = (size_t)N * N * 2, nD = (size_t)N * N * kDiffStride;
+    const size_t padW = nW + (nW & 1);  // keeps the fit rows 16-byte aligned
+    std::vector<double> t(padW + 2 * nV + nK + nD, 0.0);
+    double *tW = t.data(), *tv = tW + padW, *tc = tv + nV, *tk = tc + nV, *td = tk + nK;
+    for (int i = 0; i < N; ++i) {
+        tW[i] = W[i];
+        for (int k = 0; k < 5; ++k) {
+            tv[i * kDiffStride + k] = visc[i * 5 + k];
+            tc[i * kDiffStride + k] = cond[i * 5 + k];
+        }
+        for (int j = 0; j < N; ++j) {
+            // dfThermo.cu:40-43 (viscosity_conatant1/2), 1/sqrt(8) folded into the first
+            tk[((size_t)i * N + j) * 2 + 0] = std::pow(1.0 + W[i] / W[j], -0.5) / 2.8284271247461903;
+            tk[((size_t)i * N + j) * 2 + 1] = std::pow(W[j] / W[i], 0.25);
+            for (int k = 0; k < 5; ++k) td[((size_t)i * N + j) * kDiffStride + k] = diff[((size_t)i * N + j) * 5 + k];
+        }
+    }
+    CUDA_TRY(h, h->d_transport.ensure(t.size() * sizeof(double)));
+    CUDA_TRY(h, cudaMemcpy(h->d_transport.p, t.data(), t.size() * sizeof(double), cudaMemcpyHostToDevice));
+    const double* base = static_cast<const double*>(h->d_transport.p);
+    h->tt.N = N;
+    h->tt.W = base;
+    h->tt.visc = base + (tv - tW);
+    h->tt.cond = base + (tc - tW);
+    h->tt.wilke = base + (tk - tW);
+    h->tt.diff = base + (td - tW);
+    CUDA_TRY(h, cudaFuncSetAttribute(transport_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)transport_smem_bytes(N)));
+    return DFCHEM_OK;
+}
+
+// thermo_<mech>.txt of the reference (src_gpu/dfThermo.cu:361-435): int N; double W[N];
+// N x 15 NASA [Tmid, high7, low7]; N x 5 viscosity; N x 5 conductivity; N x N x 5 binary diffusion
+int dfchem_load_transport_file(dfchem_handle h, const char* path) {
+    if (!h || !path) return fail(h, DFCHEM_EINVAL, "dfchem_load_transport_file: bad argument");
+    FILE* fp = std::fopen(path, "rb");
+    if (!fp) return fail(h, DFCHEM_EMECH, std::string("cannot open transport coefficient file ") + path);
+    const int N = h->mech.N;
+    int n_file = 0;
+    std::vector<double> W(N), nasa((size_t)N * 15), visc((size_t)N * 5), cond((size_t)N * 5), diff((size_t)N * N * 5);
+    bool ok = std::fread(&n_file, sizeof(int), 1, fp) == 1 && n_file == N;
+    ok = ok && std::fread(W.data(), sizeof(double), W.size(), fp) == W.size();
+    ok = ok && std::fread(nasa.data(), sizeof(double), nasa.size(), fp) == nasa.size();
+    ok = ok && std::fread(visc.data(), sizeof(double), visc.size(), fp) == visc.size();
+    ok = ok && std::fread(cond.data(), sizeof(double), cond.size(), fp) == cond.size();
+    ok = ok && std::fread(diff.data(), sizeof(double), diff.size(), fp) == diff.size();
+    std::fclose(fp);
+    if (!ok) return fail(h, DFCHEM_EMECH, "transport coefficient file: species count differs from the mechanism or file truncated");
+    for (int i = 0; i < N; ++i)
+        if (std::fabs(W[i] - h->mech.W[i]) > 1e-9 * h->mech.W[i])
+            return fail(h, DFCHEM_EMECH, "transport coefficient file: molecular weights differ from the mechanism (species order?)");
+    return dfchem_set_transport_fits(h, visc.data(), cond.data(), diff.data());
+}
+
+int dfchem_transport_dev(dfchem_handle h, int n, const double* T, const double* p, const double* rho,
+                         const double* cp, const double* Y, int ldY, double* mu, double* alpha,
+                         double* rhoD, int ldD, int unity_lewis, void* stream) {
+    if (!h) return DFCHEM_EINVAL;
+    const bool need_cp = alpha || (rhoD && unity_lewis), need_rho = rhoD && !unity_lewis;
+    if (n < 0 || (n > 0 && (!T || !Y || (need_cp && !cp) || (need_rho && (!rho || !p)))) || ldY < n || (rhoD && ldD < n))
+        return fail(h, DFCHEM_EINVAL, "dfchem_transport_dev: bad argument");
+    if (h->tt.N != h->mech.N) return fail(h, DFCHEM_EINVAL, "dfchem_transport: no transport fits loaded (dfchem_set_transport_fits)");
+    if (n == 0) return DFCHEM_OK;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    const size_t smem = transport_smem_bytes(h->mech.N);
+    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / smem));
+    const int grid = std::min((n + kTransportBlock - 1) / kTransportBlock, h->sm_count * per_sm);
+    transport_kernel<<<grid, kTransportBlock, smem, static_cast<cudaStream_t>(stream)>>>(h->tt, n, T, p, rho, cp, Y, ldY, mu, alpha,
+                                                                                         rhoD, ldD, unity_lewis);
+    CUDA_TRY(h, cudaGetLastError());
+    return DFCHEM_OK;
+}
+
+int dfchem_transport(dfchem_handle h, int n, const double* T, const double* p, const double* rho, const double* cp,
+                     const double* Y, int ldY, double* mu, double* alpha, double* rhoD, int ldD, int unity_lewis) {
+    if (!h) return DFCHEM_EINVAL;
+    const bool need_cp = alpha || (rhoD && unity_lewis), need_rho = rhoD && !unity_lewis;
+    if (n < 0 || (n > 0 && (!T || !Y || (need_cp && !cp) || (need_rho && (!rho || !p)))) || ldY < n || (rhoD && ldD < n))
+        return fail(h, DFCHEM_EINVAL, "dfchem_transport: bad argument");
+    if (n == 0) return DFCHEM_OK;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    const int N = h->mech.N;
+    const size_t ld = (size_t)n, nb = ld * sizeof(double);
+    CUDA_TRY(h, h->scratch.ensure((2 * (size_t)N + 6) * nb));
+    double* d = static_cast<double*>(h->scratch.p);
+    double *dT = d, *dp = d + ld, *drho = d + 2 * ld, *dcp = d + 3 * ld, *dmu = d + 4 * ld, *dal = d + 5 * ld;
+    double *dY = d + 6 * ld, *dD = dY + (size_t)N * ld;
+    cudaStream_t s = h->streams[0];
+    CUDA_TRY(h, cudaMemcpyAsync(dT, T, nb, cudaMemcpyHostToDevice, s));
+    if (p) CUDA_TRY(h, cudaMemcpyAsync(dp, p, nb, cudaMemcpyHostToDevice, s));
+    if (rho) CUDA_TRY(h, cudaMemcpyAsync(drho, rho, nb, cudaMemcpyHostToDevice, s));
+    if (cp) CUDA_TRY(h, cudaMemcpyAsync(dcp, cp, nb, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(h, cudaMemcpy2DAsync(dY, nb, Y, (size_t)ldY * sizeof(double), nb, N, cudaMemcpyHostToDevice, s));
+    int rc = dfchem_transport_dev(h, n, dT, p ? dp : nullptr, rho ? drho : nullptr, cp ? dcp : nullptr, dY, n,
+                                  mu ? dmu : nullptr, alpha ? dal : nullptr, rhoD ? dD : nullptr, n, unity_lewis, s);
+    if (rc != DFCHEM_OK) return rc;
+    if (mu) CUDA_TRY(h, cudaMemcpyAsync(mu, dmu, nb, cudaMemcpyDeviceToHost, s));
+    if (alpha) CUDA_TRY(h, cudaMemcpyAsync(alpha, dal, nb, cudaMemcpyDeviceToHost, s));
+    if (rhoD)
+        CUDA_TRY(h, cudaMemcpy2DAsync(rhoD, (size_t)ldD * sizeof(double), dD, nb, nb, N, cudaMemcpyDeviceToHost, s));
     CUDA_TRY(h, cudaStreamSynchronize(s));
     return DFCHEM_OK;
 }

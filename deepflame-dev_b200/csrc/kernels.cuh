@@ -83,6 +83,27 @@ wdot_kernel(const DevMech mg, int nC, const double* T, const double* p, const do
     }
 }
 
+template <int NP, int NSLOT>
+__global__ void __launch_bounds__(max_warps(NP) * kTeam, 1)
+rop_kernel(const DevMech mg, int nC, const double* T, const double* p, const double* Y, int ldY,
+           const int* rorder, double* q, int ldQ, unsigned int* queue) {
+    extern __shared__ double2 dfc_smem[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>(dfc_smem);
+    const DevMech m = stage_hot_tables(mg, smem);
+    const int lane = threadIdx.x % kTeam, warp = threadIdx.x / kTeam;
+    const uint32_t cell_off = (uint32_t)m.hot_bytes + (uint32_t)warp * (uint32_t)m.cell_doubles * 8u;
+    double* sm = reinterpret_cast<double*>(smem + cell_off);
+    LaneRegs<NP, NSLOT> regs;
+    load_wdot_regs(m, &regs, lane, cell_off);
+    while (true) {
+        int cell = 0;
+        if (lane == 0) cell = (int)atomicAdd(queue, 1u);
+        cell = __shfl_sync(0xffffffffu, cell, 0);
+        if (cell >= nC) break;
+        rop_one_cell<NP, NSLOT>(m, sm, &regs, lane, T, p, Y, ldY, rorder, q, ldQ, cell);
+    }
+}
+
 // ---- thermo: thread per cell, species-major loads are coalesced across the warp ---------------
 // correctThermo cell body (dfChemistryModel.C:494-511) without transport: normalise Y, Newton on
 // T with cp as slope (setState_HP; same iteration as src_gpu/dfThermo.cu:296-320 with Cantera's

@@ -48,6 +48,15 @@ SIGNATURES = {
                                           c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "dfchem_h_from_T": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "dfchem_h_from_T_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "dfchem_rop": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int]),
+    "dfchem_rop_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]),
+    "dfchem_reaction_stoich": (c_int, [c_void_p, c_int, _dp]),
+    "dfchem_set_transport_fits": (c_int, [c_void_p, _dp, _dp, _dp]),
+    "dfchem_load_transport_file": (c_int, [c_void_p, c_char_p]),
+    "dfchem_transport": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                 c_void_p, c_void_p, c_void_p, c_int, c_int]),
+    "dfchem_transport_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                     c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "dfchem_last_counters": (c_int, [c_void_p, POINTER(c_ulonglong)]),
     "dfchem_balance_plan": (c_int, [_dp, c_int, _dp]),
     "dfchem_bench_fp64_peak": (c_int, [c_int, _dp]),
@@ -164,6 +173,62 @@ class Handle:
         he = np.empty(n)
         self.check(self.lib.dfchem_h_from_T(self.h, n, _ptr(T), _ptr(Y), Y.shape[1], _ptr(he)))
         return he
+
+
+    def rop(self, T, p, Y):
+        """Net rates of progress [R, nC] (kmol/m^3/s), reaction order of the mechanism file."""
+        nC = T.shape[0]
+        out = np.empty((self.R, nC))
+        self.check(self.lib.dfchem_rop(self.h, nC, _ptr(T), _ptr(p), _ptr(Y), Y.shape[1], _ptr(out), nC))
+        return out
+
+    def reaction_stoich(self, reaction):
+        nu = np.zeros(self.N)
+        self.check(self.lib.dfchem_reaction_stoich(self.h, int(reaction), nu.ctypes.data_as(_dp)))
+        return nu
+
+    def set_transport_fits(self, visc, cond, diff):
+        visc = np.ascontiguousarray(visc, dtype=np.float64).reshape(self.N, 5)
+        cond = np.ascontiguousarray(cond, dtype=np.float64).reshape(self.N, 5)
+        diff = np.ascontiguousarray(diff, dtype=np.float64).reshape(self.N, self.N, 5)
+        self.check(self.lib.dfchem_set_transport_fits(self.h, visc.ctypes.data_as(_dp), cond.ctypes.data_as(_dp),
+                                                      diff.ctypes.data_as(_dp)))
+
+    def load_transport_file(self, path):
+        self.check(self.lib.dfchem_load_transport_file(self.h, os.fsencode(path)))
+
+    def transport(self, T, p, rho, cp, Y, unity_lewis=False, want_mu=True, want_alpha=True, want_rhoD=True):
+        n = T.shape[0]
+        mu = np.empty(n) if want_mu else None
+        alpha = np.empty(n) if want_alpha else None
+        rhoD = np.empty((self.N, n)) if want_rhoD else None
+        self.check(self.lib.dfchem_transport(self.h, n, _ptr(T), _ptr(p), _ptr(rho), _ptr(cp), _ptr(Y), Y.shape[1],
+                                             _ptr(mu), _ptr(alpha), _ptr(rhoD), n, int(bool(unity_lewis))))
+        return mu, alpha, rhoD
+
+
+def read_thermo_file(path):
+    """Parse the reference's thermo_<mech>.txt (src_gpu/dfThermo.cu:361-435): int N; W[N];
+    N x 15 NASA [Tmid, high7, low7]; N x 5 viscosity; N x 5 conductivity; N x N x 5 diffusion."""
+    raw = open(path, "rb").read()
+    N = int(np.frombuffer(raw[:4], dtype=np.int32)[0])
+    a = np.frombuffer(raw[4:], dtype=np.float64)
+    if a.size != N + 15 * N + 10 * N + 5 * N * N:
+        raise DfchemError(f"{path}: size does not match N = {N}")
+    o = 0
+    out = {}
+    for key, shape in (("W", (N,)), ("nasa", (N, 15)), ("visc", (N, 5)), ("cond", (N, 5)), ("diff", (N, N, 5))):
+        cnt = int(np.prod(shape))
+        out[key] = a[o:o + cnt].reshape(shape).copy()
+        o += cnt
+    return out
+
+
+def write_thermo_file(path, W, nasa, visc, cond, diff):
+    with open(path, "wb") as f:
+        f.write(np.int32(len(W)).tobytes())
+        for a in (W, nasa, visc, cond, diff):
+            f.write(np.ascontiguousarray(a, dtype=np.float64).tobytes())
 
 
 def balance_plan(loads):

@@ -10,6 +10,8 @@ Reference (read-only): src/dfChemistryModel/dfChemistryModel.{H,C}
   correctThermo    .C:418-543  T from (ha, p, Y); psi = W/(R T); rho = p psi
   updateEnergy     .H:326-352  he = h_mass(T, p, Y)
   calculateW       .C:897-923  wrate_i = wdot_i W_i
+  calculateRR      .C:925-987  one reaction projected on one species
+  correctThermo transport .C:513-541  mu, alpha = lambda/cp, rhoD_i (UnityLewis: = alpha), hai_i
 """
 from __future__ import annotations
 
@@ -23,8 +25,15 @@ class DfChemistryModel:
     T, p, rho, he (absolute enthalpy `ha`), psi, Y.  They play the role of the volScalarFields
     the reference class holds references to (dfChemistryModel.H:100-131)."""
 
-    def __init__(self, mechanism_file, n_cells, *, chemistry=True, rel_tol=1e-9, abs_tol=1e-15, device=0):
+    def __init__(self, mechanism_file, n_cells, *, chemistry=True, rel_tol=1e-9, abs_tol=1e-15, device=0,
+                 transport_file=None, transport_model="Mix"):
         self._h = Handle(mechanism_file, device)
+        # transport fits in the reference's thermo_<mech>.txt layout (src_gpu/dfThermo.cu:361-435);
+        # transport_model mirrors CanteraMixture::transportModelName ("Mix" | "UnityLewis")
+        self.transportModelName_ = transport_model
+        self._has_transport = transport_file is not None
+        if self._has_transport:
+            self._h.load_transport_file(transport_file)
         self.chemistry_ = bool(chemistry)
         self.relTol_, self.absTol_ = float(rel_tol), float(abs_tol)
         self._h.set_tolerances(self.relTol_, self.absTol_)
@@ -37,6 +46,10 @@ class DfChemistryModel:
         self._Y = np.zeros((N, n))
         self._RR = np.zeros((N, n))
         self._wrate = np.zeros((N, n))
+        self.mu = np.zeros(n)
+        self.alpha = np.zeros(n)
+        self._rhoD = np.zeros((N, n))
+        self._hai = np.zeros((N, n))
         self._Qdot = np.zeros(n)
         self.cpuTimes_ = np.zeros(n)       # per-cell cost (step attempts); ChemistrySolution::cpuTime analogue
         self.cellStatus_ = np.zeros(n, dtype=np.int32)
@@ -84,11 +97,32 @@ class DfChemistryModel:
         return min(result, 2.0 * float(deltaT)) if scalar else result
 
     def correctThermo(self):
-        """T from (he, p, Y) by Newton; psi and rho updated (dfChemistryModel.C:494-511)."""
-        T, psi, rho, _, _ = self._h.correct_thermo(self.he, self.p, self._Y, self.T)
+        """T from (he, p, Y) by Newton; psi and rho updated (dfChemistryModel.C:494-511); with
+        transport fits loaded also mu, alpha, rhoD_i and hai_i (dfChemistryModel.C:513-541)."""
+        tr = self._has_transport
+        T, psi, rho, cp, hai = self._h.correct_thermo(self.he, self.p, self._Y, self.T, want_cp=tr, want_hai=tr)
         self.T[:] = T
         self.psi[:] = psi
         self.rho[:] = rho
+        if tr:
+            mu, alpha, rhoD = self._h.transport(self.T, self.p, self.rho, cp, self._Y,
+                                                unity_lewis=self.transportModelName_ == "UnityLewis")
+            self.mu[:] = mu
+            self.alpha[:] = alpha
+            self._rhoD[:] = rhoD
+            self._hai[:] = hai
+
+    def rhoD(self, i):
+        return self._rhoD[i]
+
+    def hai(self, i):
+        return self._hai[i]
+
+    def calculateRR(self, reactionI, speciei):
+        """Net rate of reaction `reactionI` projected on species `speciei` [kg/m^3/s]
+        (dfChemistryModel.C:925-987)."""
+        q = self._h.rop(self.T, self.p, self._Y)[reactionI]
+        return self._h.reaction_stoich(reactionI)[speciei] * q * self._h.W[speciei]
 
     def updateEnergy(self):
         self.he[:] = self._h.h_from_T(self.T, self._Y)

@@ -67,3 +67,30 @@ def make_batch(name, species, W, n_cells, seed=12345, burning_fraction=0.5, T_ra
     wbar = 1.0 / (Y / W[None, :]).sum(1)
     rho = p * wbar / (R_GAS * T)
     return dict(T=T, p=p, rho=rho, Y=np.ascontiguousarray(Y.T))
+
+
+def synthetic_transport_fits(W, seed=7):
+    """Plausible fits for mechanisms without a coefficient file: the hard-sphere forms
+    mu ~ sqrt(W T)/sigma^2, lambda ~ mu cv-like / W, D_ij ~ T^1.5 sqrt(1/W_i + 1/W_j)/sigma_ij^2 with a
+    small ln T dependence; symmetric in (i, j) as Cantera's are."""
+    rng = np.random.default_rng(seed)
+    W = np.asarray(W, float)
+    N = W.shape[0]
+    sig = rng.uniform(2.5, 5.0, N)
+    visc = np.zeros((N, 5))
+    cond = np.zeros((N, 5))
+    diff = np.zeros((N, N, 5))
+    visc[:, 0] = np.sqrt(2.67e-6 * np.sqrt(W) / sig**2)
+    visc[:, 1] = visc[:, 0] * rng.uniform(0.01, 0.05, N)
+    visc[:, 2] = -visc[:, 0] * rng.uniform(0.0, 0.003, N)
+    cond[:, 0] = 2.67e-6 * np.sqrt(W) / sig**2 * 3.0e4 / W
+    cond[:, 1] = cond[:, 0] * rng.uniform(0.02, 0.1, N)
+    cond[:, 3] = cond[:, 0] * rng.uniform(0.0, 1e-4, N)
+    sij = 0.5 * (sig[:, None] + sig[None, :])
+    d0 = 2.6e-2 * np.sqrt(0.5 * (1.0 / W[:, None] + 1.0 / W[None, :])) / sij**2
+    e1 = rng.uniform(0.01, 0.04, (N, N))
+    e1 = 0.5 * (e1 + e1.T)
+    diff[:, :, 0] = d0
+    diff[:, :, 1] = d0 * e1
+    diff[:, :, 4] = -d0 * 1e-5
+    return visc, cond, diff

@@ -115,6 +115,35 @@ int dfchem_h_from_T(dfchem_handle h, int n, const double* T, const double* Y, in
 int dfchem_h_from_T_dev(dfchem_handle h, int n, const double* T, const double* Y, int ldY,
                         double* he, void* stream);
 
+/* Net rates of progress q[r*ldQ + c] [kmol/m^3/s] of every reaction r (order of the mechanism
+ * file) at (T, p, Y): the CanteraKinetics_->getNetRatesOfProgress call of calculateRR
+ * (dfChemistryModel.C:925-987).  calculateRR(reactionI, speciei) is nu_net[speciei] * q[reactionI]
+ * * W[speciei] with nu_net from dfchem_reaction_stoich (products minus reactants,
+ * dfChemistryModel.C:967-982). */
+int dfchem_rop(dfchem_handle h, int nC, const double* T, const double* p, const double* Y,
+               int ldY, double* q, int ldQ);
+int dfchem_rop_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* Y,
+                   int ldY, double* q, int ldQ, void* stream);
+int dfchem_reaction_stoich(dfchem_handle h, int reaction, double* nu_net /* [N] */);
+
+/* Transport part of correctThermo (dfChemistryModel.C:513-541): mu = Wilke mixture viscosity
+ * [Pa s], alpha = lambda_mix / cp [kg/m/s], rhoD[i*ldD + c] = rho * D_i^mix [kg/m/s] (mass-flux
+ * mixture-averaged form, getMixDiffCoeffsMass) or = alpha when unity_lewis != 0
+ * (dfChemistryModel.C:521-527).  The species fits are Cantera's polynomials in ln T, supplied in
+ * the layout of the reference's thermo_<mech>.txt (src_gpu/dfThermo.cu:361-435): visc[N][5],
+ * cond[N][5], diff[N][N][5]; evaluation follows src_gpu/dfThermo.cu:111-255.  Any of mu, alpha,
+ * rhoD may be NULL; cp [J/kg/K] (from dfchem_correct_thermo) is read for alpha, rho and p for
+ * rhoD. */
+int dfchem_set_transport_fits(dfchem_handle h, const double* visc, const double* cond,
+                              const double* diff);
+int dfchem_load_transport_file(dfchem_handle h, const char* thermo_txt_path);
+int dfchem_transport(dfchem_handle h, int n, const double* T, const double* p, const double* rho,
+                     const double* cp, const double* Y, int ldY, double* mu, double* alpha,
+                     double* rhoD, int ldD, int unity_lewis);
+int dfchem_transport_dev(dfchem_handle h, int n, const double* T, const double* p,
+                         const double* rho, const double* cp, const double* Y, int ldY, double* mu,
+                         double* alpha, double* rhoD, int ldD, int unity_lewis, void* stream);
+
 /* Counters of the last dfchem_solve or dfchem_solve_dev call, summed over its cells (the _dev
  * form must be synchronised by the caller first): [0] accepted steps, [1] rejected steps,
  * [2] cells with status != 0, [3] kernel launches issued by the last call. */
