@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -56,6 +57,7 @@ struct dfchem_ctx {
     int* d_rorder = nullptr;                  // [R] internal -> caller's reaction index (rop kernel)
     DevBuf d_transport;                       // transport fit tables (dfchem_set_transport_fits)
     TransportTab tt{};
+    int thermo_ctas = 0;                      // resident thermo_kernel CTAs per SM (occupancy query, cached)
     std::string err;
 };
 
@@ -385,9 +387,16 @@ int dfchem_correct_thermo_dev(dfchem_handle h, int n, const double* he, const do
     if (n == 0) return DFCHEM_OK;
     CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    const int N = h->mech.N, grid = std::min((n + 255) / 256, h->sm_count * 8);
+    const int N = h->mech.N;
     const size_t tsm = thermo_smem_bytes(N);
     if (tsm > 48 * 1024) return fail(h, DFCHEM_EUNSUPPORTED, "thermo kernel: species tables exceed 48 KB of shared memory");
+    if (h->thermo_ctas == 0) {  // persistent CTAs: two waves of what is resident (the measured configuration)
+        int nb = 0;
+        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, thermo_kernel, 256, tsm));
+        h->thermo_ctas = std::max(1, nb);
+    }
+    static const int waves_env = [] { const char* e = std::getenv("DFCHEM_THERMO_WAVES"); return e ? std::max(1, std::atoi(e)) : 2; }();
+    const int grid = std::min((n + 255) / 256, h->sm_count * h->thermo_ctas * waves_env);
     thermo_kernel<<<grid, 256, tsm, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
     CUDA_TRY(h, cudaGetLastError());
     return DFCHEM_OK;
@@ -579,8 +588,13 @@ int dfchem_transport_dev(dfchem_handle h, int n, const double* T, const double* 
     if (n == 0) return DFCHEM_OK;
     CUDA_TRY(h, cudaSetDevice(h->device));
     const size_t smem = transport_smem_bytes(h->mech.N);
-    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / smem));
-    const int grid = std::min((n + kTransportBlock - 1) / kTransportBlock, h->sm_count * per_sm);
+    // CTAs per SM: as many as shared memory and registers allow (8).  A sweep (profiles/r1, gri30, 4M cells)
+    // of 3/4/5/6/8 CTAs per SM gave 28.9/27.2/23.2/22.2/19.4 ms: the kernel is latency-bound, so resident
+    // warps count for more than keeping the N^2 x 64-byte fit tables L1-resident.
+    static const int per_sm_env = [] { const char* e = std::getenv("DFCHEM_TR_CTAS"); return e ? std::atoi(e) : 0; }();
+    int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / smem));
+    if (per_sm_env > 0) per_sm = per_sm_env;
+    const int grid = std::min((n + kTransportCells - 1) / kTransportCells, h->sm_count * per_sm);
     transport_kernel<<<grid, kTransportBlock, smem, static_cast<cudaStream_t>(stream)>>>(h->tt, n, T, p, rho, cp, Y, ldY, mu, alpha,
                                                                                          rhoD, ldD, unity_lewis);
     CUDA_TRY(h, cudaGetLastError());

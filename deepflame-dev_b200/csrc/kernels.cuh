@@ -116,48 +116,117 @@ rop_kernel(const DevMech mg, int nC, const double* T, const double* p, const dou
 // then costs a dozen flops per iteration instead of two polynomial evaluations per species; a
 // final check re-runs the pass in the rare case that the root sits on the other side of some
 // species' T_mid.  Nothing composition-sized is kept in registers, so occupancy is high.
-// Tables in shared memory: per species 16 doubles [range][a0..a6, 0] (range offset 64 B), then
-// 1/W, T_mid and the caller's species index.
+// Tables in shared memory, in the CALLER's species order (no index indirection in the loop).  The
+// mechanism's distinct switch temperatures T_sw[0] < T_sw[1] < ... cut the T axis into n_sw + 1
+// intervals; for every species and interval the record [a0/W .. a5/W, 1/W, T_mid] of the NASA range
+// that holds there is stored (pre-divided by the molecular weight, so a species contributes
+// y * record), which makes the range selection ONE decision per cell -- the interval of Tsel --
+// instead of one per species.  Mechanisms with more than kThermoMaxSw switch temperatures fall
+// back to a per-species test on a two-slot [low, high] table.
 constexpr int kThermoBatch = 12;
+constexpr int kThermoMaxSw = 3;
 struct ThermoSmem {
-    const double* nasa;   // [N][2][8]
-    const double* rW;     // [N]
-    const double* Tmid;   // [N]
-    const double* Tsw;    // [n_sw] distinct T_mid values (usually one or two)
-    const int* perm;      // [N]
+    const double* rec;    // [N][slots][8]
+    const double* Tsw;    // [n_sw] distinct T_mid values, ascending
     int n_sw;
+    int slots;            // n_sw + 1 (interval table) or 2 (per-species fallback)
+    bool by_interval;
 };
 __device__ __forceinline__ ThermoSmem stage_thermo_tables(const DevMech& m, double* smem) {
     const int N = m.N;
-    double* nasa = smem;
-    double* rW = nasa + (size_t)N * 16;
-    double* Tmid = rW + N;
-    double* Tsw = Tmid + N;
-    int* perm = reinterpret_cast<int*>(Tsw + N);
-    int* n_sw = perm + N;
-    for (int i = threadIdx.x; i < N * 16; i += blockDim.x) {
-        const int k = i >> 4, r = (i >> 3) & 1, j = i & 7;
-        nasa[i] = j < 7 ? __ldg(m.nasa + (size_t)k * 14 + r * 7 + j) : 0.0;
-    }
-    for (int k = threadIdx.x; k < N; k += blockDim.x) {
-        rW[k] = 1.0 / __ldg(m.W + k);
-        Tmid[k] = __ldg(m.Tmid + k);
-        perm[k] = __ldg(m.perm + k);
-    }
-    if (threadIdx.x == 0) {  // distinct switch temperatures: the range-consistency test only needs these
+    double* Tsw = smem;                                   // [N] (at most N distinct values)
+    int* meta = reinterpret_cast<int*>(Tsw + N);          // n_sw
+    double* rec = Tsw + ((N + 3) & ~1);                  // 16-byte aligned records
+    if (threadIdx.x == 0) {  // distinct switch temperatures, ascending (insertion sort; N is small)
         int cnt = 0;
         for (int k = 0; k < N; ++k) {
             const double tm = __ldg(m.Tmid + k);
             bool seen = false;
             for (int j = 0; j < cnt; ++j) seen = seen || Tsw[j] == tm;
-            if (!seen) Tsw[cnt++] = tm;
+            if (seen) continue;
+            int pos = cnt++;
+            while (pos > 0 && Tsw[pos - 1] > tm) {
+                Tsw[pos] = Tsw[pos - 1];
+                --pos;
+            }
+            Tsw[pos] = tm;
         }
-        *n_sw = cnt;
+        meta[0] = cnt;
     }
     __syncthreads();
-    return ThermoSmem{nasa, rW, Tmid, Tsw, perm, *n_sw};
+    const int n_sw = meta[0];
+    const bool by_interval = n_sw <= kThermoMaxSw;
+    const int slots = by_interval ? n_sw + 1 : 2;
+    for (int i = threadIdx.x; i < N * slots * 8; i += blockDim.x) {
+        const int k = i / (slots * 8), sl = (i >> 3) % slots, j = i & 7;
+        const double tmid = __ldg(m.Tmid + k);
+        // interval sl = (T_sw[sl-1], T_sw[sl]]: the low range holds iff T <= T_mid, i.e. iff T_sw[sl] <= T_mid
+        const int hi = by_interval ? ((sl < n_sw && Tsw[sl] <= tmid) ? 0 : 1) : sl;
+        const double rw = 1.0 / __ldg(m.W + k);
+        const double v = j < 6 ? __ldg(m.nasa + (size_t)k * 14 + hi * 7 + j) * rw : (j == 6 ? rw : tmid);
+        rec[((size_t)__ldg(m.perm + k) * slots + sl) * 8 + j] = v;
+    }
+    __syncthreads();
+    return ThermoSmem{rec, Tsw, n_sw, slots, by_interval};
 }
-inline size_t thermo_smem_bytes(int N) { return (size_t)N * (16 + 3) * sizeof(double) + (size_t)(N + 1) * sizeof(int) + 16; }
+inline size_t thermo_smem_bytes(int N) { return ((size_t)N * (kThermoMaxSw + 1) * 8 + ((N + 3) & ~1)) * sizeof(double); }
+
+// record of species k for temperature Tq (hai / enthalpy loops: one species at a time)
+__device__ __forceinline__ const double* thermo_record(const ThermoSmem& t, int k, double Tq, int interval) {
+    const double* r = t.rec + (size_t)k * t.slots * 8;
+    return t.by_interval ? r + interval * 8 : r + ((Tq <= r[7]) ? 0 : 8);
+}
+__device__ __forceinline__ int thermo_interval(const ThermoSmem& t, double Tq) {
+    int s = 0;
+    for (int j = 0; j < t.n_sw; ++j) s += (Tq > t.Tsw[j]) ? 1 : 0;
+    return s;
+}
+
+// One pass over the species of a cell: B_j = sum_k y_k a_jk / W_k (j = 0..5), sum y, sum y/W, with
+// the NASA range of every species selected at Tsel.
+// (A software-pipelined form -- batches of 6 in ping-pong buffers, the next cell's first batch issued
+// before the Newton iteration -- measured 25 % SLOWER on B200 at 64 and at 80 registers, profiles/r1
+// README: the extra live registers and predicated tails cost more than the overlap returned.)
+template <bool UNI>
+__device__ __forceinline__ void thermo_species_pass(const ThermoSmem& t, int N, const double* __restrict__ Yc,
+                                                    size_t ldY, double Tsel, double (&B)[6], double& ysum,
+                                                    double& rw) {
+    const int stride = t.slots * 8;
+    const double* rb = t.rec + (UNI ? thermo_interval(t, Tsel) * 8 : 0);
+    double b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0, b4 = 0.0, b5 = 0.0, ys = 0.0, rs = 0.0;
+    auto accumulate = [&](const double* r, double y) {
+        if (!UNI) r += (Tsel <= r[7]) ? 0 : 8;
+        const double2* a = reinterpret_cast<const double2*>(r);
+        const double2 a01 = a[0], a23 = a[1], a45 = a[2];
+        ys += y;
+        rs = fma(y, r[6], rs);
+        b0 = fma(y, a01.x, b0);
+        b1 = fma(y, a01.y, b1);
+        b2 = fma(y, a23.x, b2);
+        b3 = fma(y, a23.y, b3);
+        b4 = fma(y, a45.x, b4);
+        b5 = fma(y, a45.y, b5);
+    };
+    // batches of kThermoBatch species: all loads of a batch are issued before its arithmetic, so
+    // that each thread keeps that many 8-byte HBM requests in flight; the species pointer advances by
+    // one row (ldY) per load instead of a 64-bit multiply per species
+    int k0 = 0;
+    const double* __restrict__ yp = Yc;
+    for (; k0 + kThermoBatch <= N; k0 += kThermoBatch) {
+        double yv[kThermoBatch];
+#pragma unroll
+        for (int u = 0; u < kThermoBatch; ++u) {
+            yv[u] = *yp;
+            yp += ldY;
+        }
+#pragma unroll
+        for (int u = 0; u < kThermoBatch; ++u) accumulate(rb + (size_t)(k0 + u) * stride, yv[u]);
+    }
+    for (; k0 < N; ++k0, yp += ldY) accumulate(rb + (size_t)k0 * stride, *yp);
+    B[0] = b0; B[1] = b1; B[2] = b2; B[3] = b3; B[4] = b4; B[5] = b5;
+    ysum = ys;
+    rw = rs;
+}
 
 __global__ void __launch_bounds__(256, 4)
 thermo_kernel(const DevMech m, int n, const double* __restrict__ he, const double* __restrict__ p,
@@ -166,6 +235,7 @@ thermo_kernel(const DevMech m, int n, const double* __restrict__ he, const doubl
     extern __shared__ double2 dfc_smem[];
     const ThermoSmem t = stage_thermo_tables(m, reinterpret_cast<double*>(dfc_smem));
     const int N = m.N;
+    const bool uni = t.by_interval;
     // persistent CTAs (grid = a few per SM): the tables are staged once per CTA, cells in a grid-stride loop
     for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
         const double htarget = he[c];
@@ -174,36 +244,15 @@ thermo_kernel(const DevMech m, int n, const double* __restrict__ he, const doubl
         double Tsel = Tc;  // temperature the NASA ranges are selected at
         double rw = 0.0, cp = 0.0;
         for (int pass = 0; pass < 4; ++pass) {
-            double ysum = 0.0, B0 = 0.0, B1 = 0.0, B2 = 0.0, B3 = 0.0, B4 = 0.0, B5 = 0.0;
-            rw = 0.0;
-            // batches of kThermoBatch species: all loads of a batch are issued before its arithmetic, so
-            // that each thread keeps that many 8-byte HBM requests in flight
-            auto accumulate = [&](int k, double y) {
-                const double2* a = reinterpret_cast<const double2*>(t.nasa + (size_t)k * 16 + (Tsel <= t.Tmid[k] ? 0 : 8));
-                const double w = y * t.rW[k];
-                const double2 a01 = a[0], a23 = a[1], a45 = a[2];
-                ysum += y;
-                rw += w;
-                B0 = fma(w, a01.x, B0);
-                B1 = fma(w, a01.y, B1);
-                B2 = fma(w, a23.x, B2);
-                B3 = fma(w, a23.y, B3);
-                B4 = fma(w, a45.x, B4);
-                B5 = fma(w, a45.y, B5);
-            };
-            int k0 = 0;
-            for (; k0 + kThermoBatch <= N; k0 += kThermoBatch) {
-                double yv[kThermoBatch];
-    #pragma unroll
-                for (int u = 0; u < kThermoBatch; ++u) yv[u] = Yc[(size_t)t.perm[k0 + u] * ldY];
-    #pragma unroll
-                for (int u = 0; u < kThermoBatch; ++u) accumulate(k0 + u, yv[u]);
-            }
-            for (; k0 < N; ++k0) accumulate(k0, Yc[(size_t)t.perm[k0] * ldY]);
+            double ysum, B[6];
+            if (uni)
+                thermo_species_pass<true>(t, N, Yc, (size_t)ldY, Tsel, B, ysum, rw);
+            else
+                thermo_species_pass<false>(t, N, Yc, (size_t)ldY, Tsel, B, ysum, rw);
             // Y is normalised by its sum (setState_PY); fold R in as well
             const double sc = kGasConstant / ysum;
             rw /= ysum;
-            B0 *= sc; B1 *= sc; B2 *= sc; B3 *= sc; B4 *= sc; B5 *= sc;
+            const double B0 = B[0] * sc, B1 = B[1] * sc, B2 = B[2] * sc, B3 = B[3] * sc, B4 = B[4] * sc, B5 = B[5] * sc;
             const double H1 = B1 * 0.5, H2 = B2 * (1.0 / 3.0), H3 = B3 * 0.25, H4 = B4 * 0.2;
             for (int it = 0; it < 60; ++it) {
                 const double h = B5 + Tc * (B0 + Tc * (H1 + Tc * (H2 + Tc * (H3 + Tc * H4))));
@@ -232,13 +281,14 @@ thermo_kernel(const DevMech m, int n, const double* __restrict__ he, const doubl
         if (cp_out) cp_out[c] = cp;
         if (hai) {
             const double RT = kGasConstant * Tc, rT = 1.0 / Tc;
+            const int iv = thermo_interval(t, Tc);
     #pragma unroll 4
             for (int k = 0; k < N; ++k) {
-                const double2* a = reinterpret_cast<const double2*>(t.nasa + (size_t)k * 16 + (Tc <= t.Tmid[k] ? 0 : 8));
+                const double2* a = reinterpret_cast<const double2*>(thermo_record(t, k, Tc, iv));
                 const double2 a01 = a[0], a23 = a[1], a45 = a[2];
                 const double hrt = a01.x + Tc * (a01.y * 0.5 + Tc * (a23.x * (1.0 / 3.0) + Tc * (a23.y * 0.25 + Tc * (a45.x * 0.2)))) +
                                    a45.y * rT;
-                hai[(size_t)t.perm[k] * ldH + c] = hrt * RT * t.rW[k];
+                hai[(size_t)k * ldH + c] = hrt * RT;  // the record holds a_j / W
             }
         }
     }
@@ -270,15 +320,16 @@ enthalpy_kernel(const DevMech m, int n, const double* __restrict__ T, const doub
     for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
         const double Tc = T[c], rT = 1.0 / Tc;
         double ysum = 0.0, h = 0.0;
+        const int iv = thermo_interval(t, Tc);
 #pragma unroll 4
         for (int k = 0; k < m.N; ++k) {
-            const double y = Y[(size_t)t.perm[k] * ldY + c];
-            const double2* a = reinterpret_cast<const double2*>(t.nasa + (size_t)k * 16 + (Tc <= t.Tmid[k] ? 0 : 8));
+            const double y = Y[(size_t)k * ldY + c];
+            const double2* a = reinterpret_cast<const double2*>(thermo_record(t, k, Tc, iv));
             const double2 a01 = a[0], a23 = a[1], a45 = a[2];
             const double hrt = a01.x + Tc * (a01.y * 0.5 + Tc * (a23.x * (1.0 / 3.0) + Tc * (a23.y * 0.25 + Tc * (a45.x * 0.2)))) +
                                a45.y * rT;
             ysum += y;
-            h = fma(y * t.rW[k], hrt, h);
+            h = fma(y, hrt, h);  // the record holds a_j / W
         }
         he[c] = h * kGasConstant * Tc / ysum;
     }

@@ -181,7 +181,7 @@ def test_rates_of_progress_match_oracle(handles, name):
     C = rho[:, None] * Yn.T / np.asarray(m.W)[None]
     qf, qr = K.rates_of_progress(m, K.RateConstants(m, T), C)
     qo = (qf - qr).T
-    scale = np.abs(qf).max(1)[None, :] + 1e-300  # per cell
+    scale = np.maximum(np.abs(qf), np.abs(qr)).max(1)[None, :] + 1e-300  # per cell: largest one-way rate
     assert (np.abs(q - qo) / scale).max() < 1e-11
     S = np.stack([h.reaction_stoich(r) for r in range(h.R)], axis=1)  # [N, R]
     assert np.array_equal(S, K.stoich_matrix(m))
