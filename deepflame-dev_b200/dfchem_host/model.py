@@ -26,11 +26,14 @@ class DfChemistryModel:
     the reference class holds references to (dfChemistryModel.H:100-131)."""
 
     def __init__(self, mechanism_file, n_cells, *, chemistry=True, rel_tol=1e-9, abs_tol=1e-15, device=0,
-                 transport_file=None, transport_model="Mix"):
+                 transport_file=None, transport_model="Mix", he_name="ha"):
         self._h = Handle(mechanism_file, device)
         # transport fits in the reference's thermo_<mech>.txt layout (src_gpu/dfThermo.cu:361-435);
         # transport_model mirrors CanteraMixture::transportModelName ("Mix" | "UnityLewis")
         self.transportModelName_ = transport_model
+        if he_name not in ("ha", "ea"):
+            raise ValueError("he_name must be 'ha' (absolute enthalpy) or 'ea' (absolute internal energy)")
+        self.heName_ = he_name             # CanteraMixture::heName (dfChemistryModel.C:495-502)
         self._has_transport = transport_file is not None
         if self._has_transport:
             self._h.load_transport_file(transport_file)
@@ -96,21 +99,42 @@ class DfChemistryModel:
             result = GREAT
         return min(result, 2.0 * float(deltaT)) if scalar else result
 
+    def _thermo_fields(self, f, fixes_value=False):
+        """Body shared by the cell loop and the patch loops of correctThermo on a dict of fields
+        (T, p, rho, he, psi, Y [+ mu, alpha, rhoD, hai]).  fixes_value: the T -> he direction of
+        fixed-temperature patches (dfChemistryModel.C:572-589), else he -> T (:494-511, :640-660)."""
+        tr = self._has_transport
+        if fixes_value:
+            h = self._h.h_from_T(f["T"], f["Y"])
+            ha = h
+        else:
+            # "ea": ha = ea + p/rho with the current rho (dfChemistryModel.C:499-502)
+            ha = f["he"] + f["p"] / f["rho"] if self.heName_ == "ea" else f["he"]
+        T, psi, rho, cp, hai = self._h.correct_thermo(np.ascontiguousarray(ha), f["p"], f["Y"], f["T"], want_cp=tr, want_hai=tr)
+        f["T"][:] = T
+        f["psi"][:] = psi
+        f["rho"][:] = rho
+        if fixes_value:  # intEnergy_mass = h - p/rho (:583-586)
+            f["he"][:] = ha - f["p"] / rho if self.heName_ == "ea" else ha
+        if tr:
+            mu, alpha, rhoD = self._h.transport(f["T"], f["p"], f["rho"], cp, f["Y"],
+                                                unity_lewis=self.transportModelName_ == "UnityLewis")
+            f["mu"][:] = mu
+            f["alpha"][:] = alpha
+            f["rhoD"][:] = rhoD
+            f["hai"][:] = hai
+
     def correctThermo(self):
         """T from (he, p, Y) by Newton; psi and rho updated (dfChemistryModel.C:494-511); with
         transport fits loaded also mu, alpha, rhoD_i and hai_i (dfChemistryModel.C:513-541)."""
-        tr = self._has_transport
-        T, psi, rho, cp, hai = self._h.correct_thermo(self.he, self.p, self._Y, self.T, want_cp=tr, want_hai=tr)
-        self.T[:] = T
-        self.psi[:] = psi
-        self.rho[:] = rho
-        if tr:
-            mu, alpha, rhoD = self._h.transport(self.T, self.p, self.rho, cp, self._Y,
-                                                unity_lewis=self.transportModelName_ == "UnityLewis")
-            self.mu[:] = mu
-            self.alpha[:] = alpha
-            self._rhoD[:] = rhoD
-            self._hai[:] = hai
+        self._thermo_fields(dict(T=self.T, p=self.p, rho=self.rho, he=self.he, psi=self.psi, Y=self._Y, mu=self.mu,
+                                 alpha=self.alpha, rhoD=self._rhoD, hai=self._hai))
+
+    def correctThermoPatch(self, patch, fixes_value):
+        """Boundary-face part of correctThermo (dfChemistryModel.C:546-727) for one patch: `patch` is a dict of
+        face arrays T, p, rho, he, psi, Y[N, nFaces] (+ mu, alpha, rhoD, hai when transport is loaded).
+        fixes_value patches take T as given and return he (:572-589); the others solve T from he like cells."""
+        self._thermo_fields(patch, fixes_value=bool(fixes_value))
 
     def rhoD(self, i):
         return self._rhoD[i]
@@ -125,7 +149,12 @@ class DfChemistryModel:
         return self._h.reaction_stoich(reactionI)[speciei] * q * self._h.W[speciei]
 
     def updateEnergy(self):
-        self.he[:] = self._h.h_from_T(self.T, self._Y)
+        """he = HE(p, T) per cell (dfChemistryModel.H:326-352); "ea": e = h - p/rho with rho = p Wbar/(R T)."""
+        h = self._h.h_from_T(self.T, self._Y)
+        if self.heName_ == "ea":
+            Yn = self._Y / self._Y.sum(0, keepdims=True)
+            h = h - 8314.46261815324 * self.T * (Yn / self._h.W[:, None]).sum(0)
+        self.he[:] = h
 
     def calculateW(self):
         self._wrate[:] = self._h.wdot(self.T, self.p, self._Y)

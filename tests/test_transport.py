@@ -227,3 +227,51 @@ def test_model_correct_thermo_with_transport_and_calculate_rr(built, tmp_path):
     tot = sum(chem.calculateRR(r, sp) for r in range(chem.nReactions()))
     chem.calculateW()
     assert np.abs(tot - chem.wrate(sp)).max() <= 1e-10 * np.abs(chem.wrate(sp)).max()
+
+
+@pytest.mark.gpu
+def test_patch_thermo_and_internal_energy_form(built, tmp_path):
+    """Boundary-face loop of correctThermo (dfChemistryModel.C:546-727): a fixed-T patch returns he = h(T) and the
+    properties at T; a free patch solves T from he; the "ea" form round-trips through e = h - p/rho."""
+    import dfchem_host
+    from dfchem_host import DfChemistryModel
+
+    d = ref_thermo()
+    path = tmp_path / "thermo_ES80_H2-7-16.txt"
+    dfchem_host.write_thermo_file(path, d["W"], d["nasa"], d["visc"], d["cond"], d["diff"])
+    g = golden("es80")
+    n = g["T"].shape[0]
+    m = OM.deserialize(synth.load_blob("es80"))
+    Yn = np.ascontiguousarray((g["Y"] / g["Y"].sum(0, keepdims=True)).T)
+    h_ref = K.h_mass(m, g["T"], Yn)
+    rho_ref = K.density(m, g["T"], g["p"], Yn)
+    for he_name in ("ha", "ea"):
+        chem = DfChemistryModel(synth.load_blob("es80"), n, transport_file=str(path), he_name=he_name)
+
+        def fresh(T):
+            N = chem.nSpecies()
+            return dict(T=np.array(T, float), p=np.array(g["p"], float), rho=np.array(rho_ref), he=np.zeros(n), psi=np.zeros(n),
+                        Y=np.ascontiguousarray(g["Y"]), mu=np.zeros(n), alpha=np.zeros(n), rhoD=np.zeros((N, n)),
+                        hai=np.zeros((N, n)))
+
+        fixed = fresh(g["T"])
+        chem.correctThermoPatch(fixed, fixes_value=True)
+        he_ref = h_ref if he_name == "ha" else h_ref - g["p"] / rho_ref
+        assert np.abs(fixed["he"] - he_ref).max() <= 1e-9 * np.abs(h_ref).max() + 1e-6
+        assert np.abs(fixed["T"] - g["T"]).max() < 1e-7
+        assert np.abs(fixed["rho"] / rho_ref - 1).max() < 1e-12
+        free = fresh(g["T"] + 40.0)
+        free["he"][:] = fixed["he"]
+        chem.correctThermoPatch(free, fixes_value=False)
+        assert np.abs(free["T"] - g["T"]).max() < 1e-6
+        assert np.abs(free["mu"] / fixed["mu"] - 1).max() < 1e-9
+        # cell form in the same energy variable
+        chem.T[:] = g["T"]
+        chem.p[:] = g["p"]
+        chem.rho[:] = rho_ref
+        chem.Y()[:] = g["Y"]
+        chem.updateEnergy()
+        assert np.abs(chem.he - he_ref).max() <= 1e-9 * np.abs(h_ref).max() + 1e-6
+        chem.T[:] = g["T"] - 35.0
+        chem.correctThermo()
+        assert np.abs(chem.T - g["T"]).max() < 1e-6
