@@ -123,7 +123,13 @@ rop_kernel(const DevMech mg, int nC, const double* T, const double* p, const dou
 // y * record), which makes the range selection ONE decision per cell -- the interval of Tsel --
 // instead of one per species.  Mechanisms with more than kThermoMaxSw switch temperatures fall
 // back to a per-species test on a two-slot [low, high] table.
-constexpr int kThermoBatch = 12;
+#ifndef DFC_THERMO_BATCH
+#define DFC_THERMO_BATCH 12
+#endif
+#ifndef DFC_THERMO_MINB
+#define DFC_THERMO_MINB 4
+#endif
+constexpr int kThermoBatch = DFC_THERMO_BATCH;
 constexpr int kThermoMaxSw = 3;
 struct ThermoSmem {
     const double* rec;    // [N][slots][8]
@@ -228,7 +234,7 @@ __device__ __forceinline__ void thermo_species_pass(const ThermoSmem& t, int N, 
     rw = rs;
 }
 
-__global__ void __launch_bounds__(256, 4)
+__global__ void __launch_bounds__(256, DFC_THERMO_MINB)
 thermo_kernel(const DevMech m, int n, const double* __restrict__ he, const double* __restrict__ p,
               const double* __restrict__ Y, int ldY, double* __restrict__ T, double* __restrict__ psi,
               double* __restrict__ rho, double* __restrict__ cp_out, double* __restrict__ hai, int ldH) {
