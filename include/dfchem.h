@@ -22,6 +22,14 @@
  *   dfchem_h_from_T[_dev]    dfChemistryModel::updateEnergy, dfChemistryModel.H:326-352, and the
  *                            fixesValue(T) patches of correctThermo :572-589; device precedent
  *                            dfThermo::updateEnergy src_gpu/dfThermo.cu:557-570
+ *   dfchem_transport[_dev]   transport part of correctThermo, dfChemistryModel.C:513-541 (mu, alpha,
+ *                            rhoD; UnityLewis :521-527); device precedent calculateViscosityGPU /
+ *                            calculateThermoConductivityGPU / calculateRhoDGPU,
+ *                            src_gpu/dfThermo.cu:502-536 (kernels :111-255)
+ *   dfchem_load_transport_file / dfchem_set_transport_fits   dfThermo::setConstantValue +
+ *                            initCoeffsfromBinaryFile, src_gpu/dfThermo.cu:361-435 (thermo_<mech>.txt)
+ *   dfchem_rop[_dev], dfchem_reaction_stoich   dfChemistryModel::calculateRR,
+ *                            dfChemistryModel.C:925-987 (getNetRatesOfProgress + projection)
  *   dfchem_balance_plan      LoadBalancer::getOperations (allAverage),
  *                            src/dfChemistryModel/loadBalancing/LoadBalancer.C:124-180
  *
