@@ -410,7 +410,7 @@ HostTables build_tables(const Mechanism& m) {
     L.off_q = take(R + 1);
     // dq is dead once the Jacobian row program has run (inside eval_wdot<true>, before the wdot
     // rows); the partial sums, the stage vector and the Gauss-Jordan pivot-row buffer reuse it
-    const int dq_need = std::max(n_dq + 1, N);
+    const int dq_need = std::max(std::max(n_dq + 1, N), 2 * R + 2);  // also holds the (forward, reverse) rate pairs of rop_one_cell
     const int alias_need = ((std::max(n_part, 1) + 1) & ~1) + ((NP + 1) & ~1) + 2 * (NP + 6);  // row: 2 pivot records
     L.off_dq = take(std::max(dq_need, alias_need));
     {

@@ -23,6 +23,7 @@ struct SolveArgs {
     int* status;   // may be nullptr
     double rtol, atol;
     int max_steps;
+    double* dtchem;  // optional in/out per-cell integrator step (deltaTChem): > 0 on entry = first trial step
 };
 
 // set up c (all N species), cs (inert tail), regs.c0/dc; returns rho_ct; ysum via reference
@@ -101,7 +102,8 @@ DFC_HD void solve_one_cell(const DevMech& m, const SolveArgs& a, double* sm, Lan
     setup_rate_constants(m, sm, T, dfc_lane);
     init_const_slots(m, sm, dfc_lane);
     st = StepStats{0, 0, kCellOk};
-    if (dt > 0.0) st = integrate_cell<NP, NSLOT>(m, sm, regs, dfc_lane, dt, a.rtol, a.atol * rho_ct, a.max_steps);
+    double h_io = a.dtchem ? a.dtchem[cell] : 0.0;
+    if (dt > 0.0) st = integrate_cell<NP, NSLOT>(m, sm, regs, dfc_lane, dt, a.rtol, a.atol * rho_ct, a.max_steps, h_io);
     // RR and Qdot
     const double rho_of = a.rho[cell];
     const double scale = dt > 0.0 ? rho_of / dt : 0.0;
@@ -136,6 +138,7 @@ DFC_HD void solve_one_cell(const DevMech& m, const SolveArgs& a, double* sm, Lan
         a.Qdot[cell] = qdot;
         if (a.cost) a.cost[cell] = (double)(st.accepted + st.rejected);
         if (a.status) a.status[cell] = st.status;
+        if (a.dtchem && dt > 0.0) a.dtchem[cell] = h_io;
     }
     DFC_LANES_END
 }
@@ -160,19 +163,60 @@ DFC_HD void wdot_one_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* reg
 // Net rates of progress q_r [kmol/m^3/s] at (T, p, Y) in the caller's reaction order: the
 // getNetRatesOfProgress call of calculateRR (dfChemistryModel.C:925-987), which projects one
 // reaction on one species as (nu''_i - nu'_i) q_r W_i.  rorder: internal -> caller's index.
+// Optional outputs: qf / qr = forward / reverse rates of progress (PaSR.C:349-350) and tc = the PaSR
+// "reactionRate" chemical time scale (PaSR.C:326-380): with wf_r = (sum of product nu) qf_r and
+// wr_r = (sum of reactant nu) qr_r,  tc = sum(wf + wr) / sum(wf^2 + wr^2) * sum_i rho Y_i / W_i  (vGreat if 0),
+// rho = the caller's (OpenFOAM) density, Y the raw mass fractions.  rxnu[2r], rxnu[2r+1]: those
+// stoichiometric sums, internal reaction order.
 template <int NP, int NSLOT>
 DFC_HD void rop_one_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* regs, int dfc_lane,
                          const double* T, const double* p, const double* Y, int ldY,
-                         const int* rorder, double* q_out, int ldQ, int cell) {
+                         const int* rorder, double* q_out, double* qf_out, double* qr_out, int ldQ,
+                         const double* rxnu, const double* rho, double* tc_out, int cell) {
     double ysum;
     const double Tc = T[cell];
-    load_cell_state<NP, NSLOT>(m, sm, regs, dfc_lane, Y, ldY, cell, Tc, p[cell], ysum);
+    const double rho_ct = load_cell_state<NP, NSLOT>(m, sm, regs, dfc_lane, Y, ldY, cell, Tc, p[cell], ysum);
     setup_rate_constants(m, sm, Tc, dfc_lane);
     init_const_slots(m, sm, dfc_lane);
-    eval_wdot<false>(m, sm, sm + m.off_c, regs, dfc_lane);
+    double* cx = sm + m.off_c;
     DFC_LANES_BEGIN
-    for (int r = tl; r < m.R; r += kTeam) q_out[(size_t)DFC_LDG(rorder + r) * ldQ + cell] = sm[m.off_q + r];
+    double s = 0.0;
+    for (int k = tl; k < m.N; k += kTeam) s += cx[k];
+    DFC_LR.red = s;
+    DFC_LANES_END_NOSYNC
+    const double ctot = team_sum(regs);
+    DFC_LANES_BEGIN
+    if (tl == 0) cx[m.N + 1] = ctot;
     DFC_LANES_END
+    eval_reactions<false, true>(m, sm, cx, dfc_lane);
+    DFC_LANES_BEGIN
+    double sw = 0.0, sw2 = 0.0;
+    for (int r = tl; r < m.R; r += kTeam) {
+        const size_t o = (size_t)DFC_LDG(rorder + r) * ldQ + cell;
+        const D2 fr = ld2(sm + m.off_dq + 2 * r);
+        if (q_out) q_out[o] = sm[m.off_q + r];
+        if (qf_out) qf_out[o] = fr.x;
+        if (qr_out) qr_out[o] = fr.y;
+        if (tc_out) {
+            const double wf = DFC_LDG(rxnu + 2 * r) * fr.x, wr = DFC_LDG(rxnu + 2 * r + 1) * fr.y;
+            sw += wf + wr;
+            sw2 = fma(wf, wf, fma(wr, wr, sw2));
+        }
+    }
+    DFC_LR.red = sw;
+    DFC_LR.tmp = sw2;
+    DFC_LANES_END
+    if (tc_out) {
+        const double sumW = team_sum(regs);
+        DFC_LANES_BEGIN
+        DFC_LR.red = DFC_LR.tmp;
+        DFC_LANES_END_NOSYNC
+        const double sumW2 = team_sum(regs);
+        const double csum = rho[cell] * ysum * ctot / rho_ct;
+        DFC_LANES_BEGIN
+        if (tl == 0) tc_out[cell] = sumW2 == 0.0 ? 1.0e300 : sumW / sumW2 * csum;  // OpenFOAM's vGreat
+        DFC_LANES_END
+    }
 }
 
 }  // namespace dfchem

@@ -10,7 +10,8 @@
 // Execution model: one team of kTeam = 32 lanes (a warp) owns one cell.  Per-cell data that all
 // lanes read lives in the cell's shared-memory block (layout in DevMech); per-lane data (the
 // lane's rows of the inverse, stage vectors) lives in registers (LaneRegs).  Lanes communicate
-// ONLY through shared memory + team barriers, never shuffles, so the same source also compiles
+// through shared memory + team barriers; the only shuffles are the team reductions (team_sum), which
+// have a host form, so the same source also compiles
 // as a sequential host emulation (tests/emu) in which a "lane block" is a for-loop over lanes.
 // Code between DFC_LANES_BEGIN/END runs once per lane (`tl` = lane in team); code outside runs
 // team-uniformly (every lane computes the same value from shared memory).
@@ -387,6 +388,7 @@ inline
 #endif
 D2 pow_factor(double o, double c) {
     if (o == 1.0) return D2{c, 1.0};
+    if (o == 0.0) return D2{1.0, 0.0};  // Cantera's C_AnyN: order 0 contributes the factor 1 even at c <= 0
     if (o == 2.0) return D2{c * c, 2.0 * c};
     if (o == 3.0) return D2{c * c * c, 3.0 * c * c};
     if (c > 0.0) return D2{pow(c, o), o * pow(c, o - 1.0)};
@@ -396,7 +398,9 @@ D2 pow_factor(double o, double c) {
 // ---- rates of progress q_r (and, if JAC, the partial derivatives) ----------------------------
 // Lane-per-reaction.  Rate laws: SURVEY Appendix A.2-A.6 (Cantera GasKinetics semantics).
 // cx: [N + 2] concentrations with cx[N] = 1 (absent factor); M_s already evaluated.
-template <bool JAC>
+// FR: also store the forward and reverse rates of progress (getFwdRatesOfProgress / getRevRatesOfProgress,
+// PaSR.C:349-350) in dq[2r], dq[2r + 1] (the derivative scratch, unused without JAC).
+template <bool JAC, bool FR = false>
 DFC_HD void eval_reactions(const DevMech& m, double* sm, const double* cx, int dfc_lane) {
     (void)dfc_lane;
     const double* kfk = sm + m.off_kf;
@@ -478,6 +482,7 @@ DFC_HD void eval_reactions(const DevMech& m, double* sm, const double* cx, int d
         const double Pp = pv[0] * pv[1] * pv[2];
         const double kre = kfe * kk.y;
         q[r] = kfe * Pf - kre * Pp;
+        if (FR) st2(dq + 2 * r, kfe * Pf, kre * Pp);
         if (JAC) {
             int slot = (int)d.w;
             if (fo[0] != none) dq[slot++] = kfe * fd[0] * fv[1] * fv[2];

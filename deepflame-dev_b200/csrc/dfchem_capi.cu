@@ -38,6 +38,7 @@ struct DevBuf {
     }
 };
 constexpr int kSlots = 2;
+constexpr int kRing = 256;  // launch slots: every kernel launch gets its own work-queue word and counter record
 }  // namespace
 
 struct dfchem_ctx {
@@ -51,13 +52,24 @@ struct dfchem_ctx {
     int sm_count = 0, warps = 0;  // warps (= cells in flight) per persistent CTA
     cudaStream_t streams[kSlots] = {nullptr, nullptr};
     DevBuf slot_in[kSlots], slot_out[kSlots], scratch;
-    unsigned int* d_queue = nullptr;          // kSlots + 1 counters (last: dev API)
-    unsigned long long* d_counters = nullptr; // 3
+    unsigned int* d_queue = nullptr;          // [kRing] work-queue words, one per launch (ring)
+    unsigned long long* d_counters = nullptr; // [kRing][4] accepted, rejected, failed cells, (unused)
+    unsigned long long seq = 0;               // launches issued so far (ring position)
+    unsigned long long call_first = 0;        // first ring slot and number of solve launches of the last solve call
+    unsigned long long call_n = 0;
+    unsigned long long call_acc[3] = {0, 0, 0};  // counters already folded on the host (calls longer than the ring)
     unsigned long long launches = 0;
+    double* dtchem = nullptr;                 // dfchem_bind_deltaTChem
+    int* d_rxsum = nullptr;                   // not used on the host; see d_rxnu
+    double* d_rxnu = nullptr;                 // [2R] internal order: sum of product / reactant stoichiometric coefficients
     int* d_rorder = nullptr;                  // [R] internal -> caller's reaction index (rop kernel)
     DevBuf d_transport;                       // transport fit tables (dfchem_set_transport_fits)
     TransportTab tt{};
     int thermo_ctas = 0;                      // resident thermo_kernel CTAs per SM (occupancy query, cached)
+    HostLpc lpc;                              // lane-per-cell tables (small mechanisms)
+    void* d_lpc = nullptr;
+    LpcMech lm{};
+    int lpc_warps = 0;                        // > 0: dfchem_solve* run lpc_solve_kernel
     std::string err;
 };
 
@@ -104,10 +116,14 @@ cudaError_t configure_t(dfchem_ctx* h) {
     return nb >= 1 ? cudaSuccess : cudaErrorLaunchOutOfResources;
 }
 
+size_t lpc_smem_bytes(const dfchem_ctx* h) {
+    return (size_t)h->lm.bytes + (size_t)h->lpc_warps * kLpcLanes * h->lm.lane_doubles * sizeof(double);
+}
+
 template <int NP, int NSLOT>
-void launch_solve_t(dfchem_ctx* h, const SolveArgs& a, unsigned int* queue, cudaStream_t s) {
+void launch_solve_t(dfchem_ctx* h, const SolveArgs& a, unsigned int* queue, unsigned long long* cnt, cudaStream_t s) {
     const int grid = std::max(1, std::min(h->sm_count, (a.nC + h->warps - 1) / h->warps));
-    solve_kernel<NP, NSLOT><<<grid, h->warps * kTeam, smem_bytes(h), s>>>(h->dm, a, queue, h->d_counters);
+    solve_kernel<NP, NSLOT><<<grid, h->warps * kTeam, smem_bytes(h), s>>>(h->dm, a, queue, cnt);
 }
 template <int NP, int NSLOT>
 void launch_wdot_t(dfchem_ctx* h, int nC, const double* T, const double* p, const double* Y, int ldY,
@@ -118,18 +134,63 @@ void launch_wdot_t(dfchem_ctx* h, int nC, const double* T, const double* p, cons
 
 template <int NP, int NSLOT>
 void launch_rop_t(dfchem_ctx* h, int nC, const double* T, const double* p, const double* Y, int ldY,
-                  double* q, int ldQ, unsigned int* queue, cudaStream_t s) {
+                  double* q, double* qf, double* qr, int ldQ, const double* rho, double* tc, unsigned int* queue,
+                  cudaStream_t s) {
     const int grid = std::max(1, std::min(h->sm_count, (nC + h->warps - 1) / h->warps));
-    rop_kernel<NP, NSLOT><<<grid, h->warps * kTeam, smem_bytes(h), s>>>(h->dm, nC, T, p, Y, ldY, h->d_rorder, q, ldQ, queue);
+    rop_kernel<NP, NSLOT><<<grid, h->warps * kTeam, smem_bytes(h), s>>>(h->dm, nC, T, p, Y, ldY, h->d_rorder, q, qf, qr, ldQ,
+                                                                       h->d_rxnu, rho, tc, queue);
 }
 
-int launch_solve(dfchem_ctx* h, const SolveArgs& a, int qslot, cudaStream_t s) {
-    unsigned int* queue = h->d_queue + qslot;
-    CUDA_TRY(h, cudaMemsetAsync(queue, 0, sizeof(unsigned int), s));
-#define CALL(NP, NS) launch_solve_t<NP, NS>(h, a, queue, s)
-    DFC_DISPATCH_NP(h->dm.NP, CALL)
+// Every launch takes the next slot of the ring: its own queue word and counter record, zeroed on the
+// launching stream.  Launches of one handle on different streams therefore never share a counter.
+int take_slot(dfchem_ctx* h, cudaStream_t s, unsigned int** queue, unsigned long long** cnt) {
+    const size_t i = (size_t)(h->seq++ % kRing);
+    *queue = h->d_queue + i;
+    CUDA_TRY(h, cudaMemsetAsync(*queue, 0, sizeof(unsigned int), s));
+    if (cnt) {
+        *cnt = h->d_counters + 4 * i;
+        CUDA_TRY(h, cudaMemsetAsync(*cnt, 0, 4 * sizeof(unsigned long long), s));
+    }
+    return DFCHEM_OK;
+}
+
+void begin_solve_call(dfchem_ctx* h) {
+    h->call_first = h->seq;
+    h->call_n = 0;
+    h->call_acc[0] = h->call_acc[1] = h->call_acc[2] = 0;
+    h->launches = 0;
+}
+
+// sum the counter records of the launches of the last solve call (device must be idle for them)
+int read_call_counters(dfchem_ctx* h, unsigned long long out[3]) {
+    std::vector<unsigned long long> ring((size_t)kRing * 4);
+    CUDA_TRY(h, cudaMemcpy(ring.data(), h->d_counters, ring.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    for (int k = 0; k < 3; ++k) out[k] = h->call_acc[k];
+    for (unsigned long long j = 0; j < h->call_n; ++j) {
+        const size_t i = (size_t)((h->call_first + j) % kRing);
+        for (int k = 0; k < 3; ++k) out[k] += ring[4 * i + k];
+    }
+    return DFCHEM_OK;
+}
+
+int launch_solve(dfchem_ctx* h, const SolveArgs& a, cudaStream_t s) {
+    unsigned int* queue = nullptr;
+    unsigned long long* cnt = nullptr;
+    // the ring position of the solve launches of one call must be contiguous: nothing else launches in between
+    // (the handle is single-caller, include/dfchem.h)
+    int rc = take_slot(h, s, &queue, &cnt);
+    if (rc != DFCHEM_OK) return rc;
+    if (h->lpc_warps > 0) {
+        const int per_cta = h->lpc_warps * kLpcLanes;
+        const int grid = std::max(1, std::min(h->sm_count, (a.nC + per_cta - 1) / per_cta));
+        lpc_solve_kernel<<<grid, per_cta, lpc_smem_bytes(h), s>>>(h->lm, a, queue, cnt);
+    } else {
+#define CALL(NP, NS) launch_solve_t<NP, NS>(h, a, queue, cnt, s)
+        DFC_DISPATCH_NP(h->dm.NP, CALL)
 #undef CALL
+    }
     ++h->launches;
+    ++h->call_n;
     CUDA_TRY(h, cudaGetLastError());
     return DFCHEM_OK;
 }
@@ -166,13 +227,25 @@ int finish_create(dfchem_ctx* h, int device, dfchem_handle* out) {
     if ((e = cudaMemcpy(h->d_blob, h->ht.blob.data(), h->ht.blob.size(), cudaMemcpyHostToDevice)) != cudaSuccess)
         return bail("cudaMemcpy(tables)", e);
     h->dm = h->ht.rebase(h->d_blob);
-    if ((e = cudaMalloc(&h->d_queue, (kSlots + 1) * sizeof(unsigned int))) != cudaSuccess) return bail("cudaMalloc", e);
-    if ((e = cudaMalloc(&h->d_counters, 3 * sizeof(unsigned long long))) != cudaSuccess) return bail("cudaMalloc", e);
-    cudaMemset(h->d_counters, 0, 3 * sizeof(unsigned long long));
+    if ((e = cudaMalloc(&h->d_queue, kRing * sizeof(unsigned int))) != cudaSuccess) return bail("cudaMalloc", e);
+    if ((e = cudaMalloc(&h->d_counters, (size_t)kRing * 4 * sizeof(unsigned long long))) != cudaSuccess) return bail("cudaMalloc", e);
+    cudaMemset(h->d_counters, 0, (size_t)kRing * 4 * sizeof(unsigned long long));
     if (h->mech.R > 0) {
         if ((e = cudaMalloc(&h->d_rorder, h->mech.R * sizeof(int))) != cudaSuccess) return bail("cudaMalloc", e);
         if ((e = cudaMemcpy(h->d_rorder, h->ht.rorder.data(), h->mech.R * sizeof(int), cudaMemcpyHostToDevice)) != cudaSuccess)
             return bail("cudaMemcpy(rorder)", e);
+        // PaSR reactionRate time scale (PaSR.C:355-378): per reaction sum of product / reactant stoichiometric coefficients
+        std::vector<double> rxnu((size_t)2 * h->mech.R, 0.0);
+        for (int rn = 0; rn < h->mech.R; ++rn) {
+            const int r = h->ht.rorder[rn];
+            for (int a = 0; a < kMaxSide; ++a) {
+                if (h->mech.p_idx[r * kMaxSide + a] >= 0) rxnu[2 * rn] += h->mech.p_nu[r * kMaxSide + a];
+                if (h->mech.r_idx[r * kMaxSide + a] >= 0) rxnu[2 * rn + 1] += h->mech.r_nu[r * kMaxSide + a];
+            }
+        }
+        if ((e = cudaMalloc(&h->d_rxnu, rxnu.size() * sizeof(double))) != cudaSuccess) return bail("cudaMalloc", e);
+        if ((e = cudaMemcpy(h->d_rxnu, rxnu.data(), rxnu.size() * sizeof(double), cudaMemcpyHostToDevice)) != cudaSuccess)
+            return bail("cudaMemcpy(rxnu)", e);
     }
     for (int i = 0; i < kSlots; ++i)
         if ((e = cudaStreamCreateWithFlags(&h->streams[i], cudaStreamNonBlocking)) != cudaSuccess)
@@ -182,6 +255,32 @@ int finish_create(dfchem_ctx* h, int device, dfchem_handle* out) {
     DFC_DISPATCH_NP(h->dm.NP, CALL)
 #undef CALL
     if (e != cudaSuccess) return bail("kernel configuration", e);
+    // Lane-per-cell solve kernel.  Measured on B200 (profiles/r2): 12x the warp-per-cell kernel on the one-step
+    // C7H16 mechanism (1.98e8 vs 1.65e7 cells/s), but no faster on the 16-21-reaction H2 mechanisms, where its
+    // serial shared-memory read-modify-write chains run at one warp per scheduler.  Default: global mechanisms
+    // with at most kLpcAutoReactions reactions; DFCHEM_SOLVER=lane / warp forces either kernel (A/B runs, tests).
+    const char* solver_env = std::getenv("DFCHEM_SOLVER");
+    const std::string solver = solver_env ? solver_env : "";
+    constexpr int kLpcAutoReactions = 6;
+    if (solver == "lane" || (solver != "warp" && h->mech.R <= kLpcAutoReactions)) {
+        h->lpc = build_lpc_tables(h->mech, h->ht.perm, h->dm.NA);
+        if (h->lpc.usable) {
+            int max_optin = 0;
+            if ((e = cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device)) != cudaSuccess)
+                return bail("cudaDeviceGetAttribute", e);
+            const size_t per_warp = (size_t)kLpcLanes * h->lpc.layout.lane_doubles * sizeof(double);
+            const int warps = (int)std::min<size_t>(16, ((size_t)max_optin - h->lpc.blob.size()) / per_warp);
+            if (warps >= 2) {
+                if ((e = cudaMalloc(&h->d_lpc, h->lpc.blob.size())) != cudaSuccess) return bail("cudaMalloc(lpc tables)", e);
+                if ((e = cudaMemcpy(h->d_lpc, h->lpc.blob.data(), h->lpc.blob.size(), cudaMemcpyHostToDevice)) != cudaSuccess)
+                    return bail("cudaMemcpy(lpc tables)", e);
+                h->lm = h->lpc.rebase(h->d_lpc);
+                if ((e = cudaFuncSetAttribute(lpc_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin)) != cudaSuccess)
+                    return bail("cudaFuncSetAttribute(lpc_solve_kernel)", e);
+                h->lpc_warps = warps;
+            }
+        }
+    }
     *out = h;
     return DFCHEM_OK;
 }
@@ -235,6 +334,8 @@ void dfchem_destroy(dfchem_handle h) {
     if (h->d_queue) cudaFree(h->d_queue);
     if (h->d_counters) cudaFree(h->d_counters);
     if (h->d_rorder) cudaFree(h->d_rorder);
+    if (h->d_lpc) cudaFree(h->d_lpc);
+    if (h->d_rxnu) cudaFree(h->d_rxnu);
     h->d_transport.release();
     delete h;
 }
@@ -269,6 +370,12 @@ int dfchem_set_max_steps(dfchem_handle h, int max_steps) {
     return DFCHEM_OK;
 }
 
+int dfchem_bind_deltaTChem(dfchem_handle h, double* deltaTChem) {
+    if (!h) return DFCHEM_EINVAL;
+    h->dtchem = deltaTChem;
+    return DFCHEM_OK;
+}
+
 int dfchem_solve_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* rho,
                      const double* dt, double dt_uniform, const double* Y, int ldY, double* RR,
                      int ldRR, double* Qdot, double* cost, int* status, void* stream) {
@@ -277,13 +384,102 @@ int dfchem_solve_dev(dfchem_handle h, int nC, const double* T, const double* p, 
         return fail(h, DFCHEM_EINVAL, "dfchem_solve_dev: bad argument");
     CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    h->launches = 0;
-    CUDA_TRY(h, cudaMemsetAsync(h->d_counters, 0, 3 * sizeof(unsigned long long), s));
-    ++h->launches;
+    begin_solve_call(h);
     if (nC == 0) return DFCHEM_OK;
-    SolveArgs a{nC, T, p, rho, dt, dt_uniform, Y, ldY, RR, ldRR, Qdot, cost, status, h->rtol, h->atol, h->max_steps};
-    return launch_solve(h, a, kSlots, s);
+    SolveArgs a{nC, T, p, rho, dt, dt_uniform, Y, ldY, RR, ldRR, Qdot, cost, status, h->rtol, h->atol, h->max_steps, h->dtchem};
+    return launch_solve(h, a, s);
 }
+
+namespace {
+// Host-pointer chemistry sub-step: 2^18-cell chunks through two device staging slots on two streams
+// (H2D, kernel, D2H overlap).  Y / RR are either species-major blocks (Y, ldY) or tables of N separately
+// allocated arrays (Yptrs: the PtrList<volScalarField> of dfChemistryModel.H:105,121 as it is, no repack).
+int solve_host(dfchem_ctx* h, int nC, const double* T, const double* p, const double* rho, const double* dt,
+               double dt_uniform, const double* Y, int ldY, const double* const* Yptrs, double* RR, int ldRR,
+               double* const* RRptrs, double* Qdot, double* cost, int* status) {
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    begin_solve_call(h);
+    const int N = h->mech.N;
+    const int chunk = 1 << 18;
+    int rc = DFCHEM_OK;
+    // per-slot device staging: in = T,p,rho,dt,dtchem,Y[N];  out = RR[N],Qdot,cost,status
+    for (int i = 0, c0 = 0; c0 < nC && rc == DFCHEM_OK; ++i, c0 += chunk) {
+        const int n = std::min(chunk, nC - c0);
+        const int sl = i % kSlots;
+        cudaStream_t s = h->streams[sl];
+        const size_t ld = (size_t)chunk;
+        auto body = [&]() -> int {
+            if (h->call_n + 1 >= (unsigned long long)kRing) {  // ring about to wrap inside one call: fold on the host
+                for (int q = 0; q < kSlots; ++q) CUDA_TRY(h, cudaStreamSynchronize(h->streams[q]));
+                unsigned long long part[3];
+                int r = read_call_counters(h, part);
+                if (r != DFCHEM_OK) return r;
+                for (int k = 0; k < 3; ++k) h->call_acc[k] = part[k];
+                h->call_first = h->seq;
+                h->call_n = 0;
+            }
+            CUDA_TRY(h, h->slot_in[sl].ensure((size_t)(N + 5) * ld * sizeof(double)));
+            CUDA_TRY(h, h->slot_out[sl].ensure((size_t)(N + 3) * ld * sizeof(double)));
+            double* din = static_cast<double*>(h->slot_in[sl].p);
+            double* dout = static_cast<double*>(h->slot_out[sl].p);
+            double *dT = din, *dp = din + ld, *drho = din + 2 * ld, *ddt = din + 3 * ld, *dtc = din + 4 * ld, *dY = din + 5 * ld;
+            double *dRR = dout, *dQ = dout + (size_t)N * ld, *dcost = dQ + ld;
+            int* dstat = reinterpret_cast<int*>(dcost + ld);
+            const size_t nb = (size_t)n * sizeof(double);
+            CUDA_TRY(h, cudaMemcpyAsync(dT, T + c0, nb, cudaMemcpyHostToDevice, s));
+            CUDA_TRY(h, cudaMemcpyAsync(dp, p + c0, nb, cudaMemcpyHostToDevice, s));
+            CUDA_TRY(h, cudaMemcpyAsync(drho, rho + c0, nb, cudaMemcpyHostToDevice, s));
+            if (dt) CUDA_TRY(h, cudaMemcpyAsync(ddt, dt + c0, nb, cudaMemcpyHostToDevice, s));
+            if (h->dtchem) CUDA_TRY(h, cudaMemcpyAsync(dtc, h->dtchem + c0, nb, cudaMemcpyHostToDevice, s));
+            if (Yptrs) {
+                for (int k = 0; k < N; ++k)
+                    CUDA_TRY(h, cudaMemcpyAsync(dY + (size_t)k * ld, Yptrs[k] + c0, nb, cudaMemcpyHostToDevice, s));
+            } else {
+                CUDA_TRY(h, cudaMemcpy2DAsync(dY, ld * sizeof(double), Y + c0, (size_t)ldY * sizeof(double), nb, N,
+                                              cudaMemcpyHostToDevice, s));
+            }
+            SolveArgs a{n, dT, dp, drho, dt ? ddt : nullptr, dt_uniform, dY, (int)ld, dRR, (int)ld, dQ,
+                        cost ? dcost : nullptr, status ? dstat : nullptr, h->rtol, h->atol, h->max_steps,
+                        h->dtchem ? dtc : nullptr};
+            int r = launch_solve(h, a, s);
+            if (r != DFCHEM_OK) return r;
+            if (RRptrs) {
+                for (int k = 0; k < N; ++k)
+                    CUDA_TRY(h, cudaMemcpyAsync(RRptrs[k] + c0, dRR + (size_t)k * ld, nb, cudaMemcpyDeviceToHost, s));
+            } else {
+                CUDA_TRY(h, cudaMemcpy2DAsync(RR + c0, (size_t)ldRR * sizeof(double), dRR, ld * sizeof(double), nb, N,
+                                              cudaMemcpyDeviceToHost, s));
+            }
+            CUDA_TRY(h, cudaMemcpyAsync(Qdot + c0, dQ, nb, cudaMemcpyDeviceToHost, s));
+            if (cost) CUDA_TRY(h, cudaMemcpyAsync(cost + c0, dcost, nb, cudaMemcpyDeviceToHost, s));
+            if (status) CUDA_TRY(h, cudaMemcpyAsync(status + c0, dstat, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s));
+            if (h->dtchem) CUDA_TRY(h, cudaMemcpyAsync(h->dtchem + c0, dtc, nb, cudaMemcpyDeviceToHost, s));
+            return DFCHEM_OK;
+        };
+        rc = body();
+    }
+    // both streams are drained before returning, on the error path as well: the caller's buffers and the
+    // staging slots must not be in use by an outstanding copy once this function has returned
+    std::string first_err = h->err;
+    for (int sl = 0; sl < kSlots; ++sl) {
+        cudaError_t e = cudaStreamSynchronize(h->streams[sl]);
+        if (e != cudaSuccess && rc == DFCHEM_OK) rc = fail(h, DFCHEM_ECUDA, std::string("cudaStreamSynchronize: ") + cudaGetErrorString(e));
+    }
+    if (rc != DFCHEM_OK) {
+        if (!first_err.empty() && rc != DFCHEM_ECUDA) h->err = first_err;
+        return rc;
+    }
+    // the reference treats an integrator failure as fatal (CVODE errors propagate out of solveSingle,
+    // dfChemistryModel.C:738-780): report it even when the caller passed no status array
+    unsigned long long cnt[3];
+    rc = read_call_counters(h, cnt);
+    if (rc != DFCHEM_OK) return rc;
+    if (cnt[2] != 0)
+        return fail(h, DFCHEM_ECELLFAIL, "dfchem_solve: the integrator failed in " + std::to_string(cnt[2]) +
+                                             " cell(s) (max steps or step-size underflow); RR/Qdot of those cells are partial");
+    return DFCHEM_OK;
+}
+}  // namespace
 
 int dfchem_solve(dfchem_handle h, int nC, const double* T, const double* p, const double* rho,
                  const double* dt, double dt_uniform, const double* Y, int ldY, double* RR, int ldRR,
@@ -291,49 +487,25 @@ int dfchem_solve(dfchem_handle h, int nC, const double* T, const double* p, cons
     if (!h) return DFCHEM_EINVAL;
     if (nC < 0 || (nC > 0 && (!T || !p || !rho || !Y || !RR || !Qdot)) || ldY < nC || ldRR < nC)
         return fail(h, DFCHEM_EINVAL, "dfchem_solve: bad argument");
-    CUDA_TRY(h, cudaSetDevice(h->device));
-    h->launches = 0;
-    CUDA_TRY(h, cudaMemset(h->d_counters, 0, 3 * sizeof(unsigned long long)));
-    const int N = h->mech.N;
-    const int chunk = 1 << 18;
-    // per-slot device staging: in = T,p,rho,dt,Y[N];  out = RR[N],Qdot,cost,status
-    for (int i = 0, c0 = 0; c0 < nC; ++i, c0 += chunk) {
-        const int n = std::min(chunk, nC - c0);
-        const int sl = i % kSlots;
-        cudaStream_t s = h->streams[sl];
-        const size_t ld = (size_t)chunk;
-        CUDA_TRY(h, h->slot_in[sl].ensure((size_t)(N + 4) * ld * sizeof(double)));
-        CUDA_TRY(h, h->slot_out[sl].ensure((size_t)(N + 3) * ld * sizeof(double)));
-        double* din = static_cast<double*>(h->slot_in[sl].p);
-        double* dout = static_cast<double*>(h->slot_out[sl].p);
-        double *dT = din, *dp = din + ld, *drho = din + 2 * ld, *ddt = din + 3 * ld, *dY = din + 4 * ld;
-        double *dRR = dout, *dQ = dout + (size_t)N * ld, *dcost = dQ + ld;
-        int* dstat = reinterpret_cast<int*>(dcost + ld);
-        const size_t nb = (size_t)n * sizeof(double);
-        CUDA_TRY(h, cudaMemcpyAsync(dT, T + c0, nb, cudaMemcpyHostToDevice, s));
-        CUDA_TRY(h, cudaMemcpyAsync(dp, p + c0, nb, cudaMemcpyHostToDevice, s));
-        CUDA_TRY(h, cudaMemcpyAsync(drho, rho + c0, nb, cudaMemcpyHostToDevice, s));
-        if (dt) CUDA_TRY(h, cudaMemcpyAsync(ddt, dt + c0, nb, cudaMemcpyHostToDevice, s));
-        CUDA_TRY(h, cudaMemcpy2DAsync(dY, ld * sizeof(double), Y + c0, (size_t)ldY * sizeof(double), nb, N,
-                                      cudaMemcpyHostToDevice, s));
-        SolveArgs a{n, dT, dp, drho, dt ? ddt : nullptr, dt_uniform, dY, (int)ld, dRR, (int)ld, dQ,
-                    cost ? dcost : nullptr, status ? dstat : nullptr, h->rtol, h->atol, h->max_steps};
-        int rc = launch_solve(h, a, sl, s);
-        if (rc != DFCHEM_OK) return rc;
-        CUDA_TRY(h, cudaMemcpy2DAsync(RR + c0, (size_t)ldRR * sizeof(double), dRR, ld * sizeof(double), nb, N,
-                                      cudaMemcpyDeviceToHost, s));
-        CUDA_TRY(h, cudaMemcpyAsync(Qdot + c0, dQ, nb, cudaMemcpyDeviceToHost, s));
-        if (cost) CUDA_TRY(h, cudaMemcpyAsync(cost + c0, dcost, nb, cudaMemcpyDeviceToHost, s));
-        if (status) CUDA_TRY(h, cudaMemcpyAsync(status + c0, dstat, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s));
-    }
-    for (int sl = 0; sl < kSlots; ++sl) CUDA_TRY(h, cudaStreamSynchronize(h->streams[sl]));
-    return DFCHEM_OK;
+    return solve_host(h, nC, T, p, rho, dt, dt_uniform, Y, ldY, nullptr, RR, ldRR, nullptr, Qdot, cost, status);
+}
+
+int dfchem_solve_ptrs(dfchem_handle h, int nC, const double* T, const double* p, const double* rho,
+                      const double* dt, double dt_uniform, const double* const* Yptrs, double* const* RRptrs,
+                      double* Qdot, double* cost, int* status) {
+    if (!h) return DFCHEM_EINVAL;
+    bool ok = nC >= 0 && (nC == 0 || (T && p && rho && Yptrs && RRptrs && Qdot));
+    if (ok && nC > 0)
+        for (int k = 0; k < h->mech.N; ++k) ok = ok && Yptrs[k] && RRptrs[k];
+    if (!ok) return fail(h, DFCHEM_EINVAL, "dfchem_solve_ptrs: bad argument");
+    return solve_host(h, nC, T, p, rho, dt, dt_uniform, nullptr, 0, Yptrs, nullptr, 0, RRptrs, Qdot, cost, status);
 }
 
 int dfchem_last_counters(dfchem_handle h, unsigned long long out[4]) {
     if (!h || !out) return DFCHEM_EINVAL;
     CUDA_TRY(h, cudaSetDevice(h->device));
-    CUDA_TRY(h, cudaMemcpy(out, h->d_counters, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    int rc = read_call_counters(h, out);
+    if (rc != DFCHEM_OK) return rc;
     out[3] = h->launches;
     return DFCHEM_OK;
 }
@@ -346,8 +518,11 @@ int dfchem_wdot_dev(dfchem_handle h, int nC, const double* T, const double* p, c
     if (nC == 0) return DFCHEM_OK;
     CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    unsigned int* queue = h->d_queue + kSlots;
-    CUDA_TRY(h, cudaMemsetAsync(queue, 0, sizeof(unsigned int), s));
+    unsigned int* queue = nullptr;
+    {
+        int rc = take_slot(h, s, &queue, nullptr);
+        if (rc != DFCHEM_OK) return rc;
+    }
 #define CALL(NP, NS) launch_wdot_t<NP, NS>(h, nC, T, p, Y, ldY, wrate, ldW, queue, s)
     DFC_DISPATCH_NP(h->dm.NP, CALL)
 #undef CALL
@@ -464,45 +639,93 @@ int dfchem_h_from_T(dfchem_handle h, int n, const double* T, const double* Y, in
     return DFCHEM_OK;
 }
 
-// ---- rates of progress (calculateRR, dfChemistryModel.C:925-987) --------------------------------
-int dfchem_rop_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* Y, int ldY,
-                   double* q, int ldQ, void* stream) {
-    if (!h) return DFCHEM_EINVAL;
-    if (nC < 0 || (nC > 0 && (!T || !p || !Y || !q)) || ldY < nC || ldQ < nC)
-        return fail(h, DFCHEM_EINVAL, "dfchem_rop_dev: bad argument");
+// ---- rates of progress (calculateRR, dfChemistryModel.C:925-987; PaSR.C:326-385) ------------------
+namespace {
+int rop_dev_impl(dfchem_ctx* h, const char* who, int nC, const double* T, const double* p, const double* Y, int ldY,
+                 double* q, double* qf, double* qr, int ldQ, const double* rho, double* tc, cudaStream_t s) {
+    if (nC < 0 || (nC > 0 && (!T || !p || !Y)) || ldY < nC || ((q || qf || qr) && ldQ < nC) || (tc && !rho))
+        return fail(h, DFCHEM_EINVAL, std::string(who) + ": bad argument");
     if (nC == 0 || h->mech.R == 0) return DFCHEM_OK;
     CUDA_TRY(h, cudaSetDevice(h->device));
-    cudaStream_t s = static_cast<cudaStream_t>(stream);
-    unsigned int* queue = h->d_queue + kSlots;
-    CUDA_TRY(h, cudaMemsetAsync(queue, 0, sizeof(unsigned int), s));
-#define CALL(NP, NS) launch_rop_t<NP, NS>(h, nC, T, p, Y, ldY, q, ldQ, queue, s)
+    unsigned int* queue = nullptr;
+    int rc = take_slot(h, s, &queue, nullptr);
+    if (rc != DFCHEM_OK) return rc;
+#define CALL(NP, NS) launch_rop_t<NP, NS>(h, nC, T, p, Y, ldY, q, qf, qr, ldQ, rho, tc, queue, s)
     DFC_DISPATCH_NP(h->dm.NP, CALL)
 #undef CALL
     CUDA_TRY(h, cudaGetLastError());
     return DFCHEM_OK;
 }
 
-int dfchem_rop(dfchem_handle h, int nC, const double* T, const double* p, const double* Y, int ldY,
-               double* q, int ldQ) {
-    if (!h) return DFCHEM_EINVAL;
-    if (nC < 0 || (nC > 0 && (!T || !p || !Y || !q)) || ldY < nC || ldQ < nC)
-        return fail(h, DFCHEM_EINVAL, "dfchem_rop: bad argument");
+// host-pointer wrapper: stages T, p, rho, Y in; up to three [R][nC] blocks and tc out
+int rop_host_impl(dfchem_ctx* h, const char* who, int nC, const double* T, const double* p, const double* rho,
+                  const double* Y, int ldY, double* q, double* qf, double* qr, int ldQ, double* tc) {
+    if (nC < 0 || (nC > 0 && (!T || !p || !Y)) || ldY < nC || ((q || qf || qr) && ldQ < nC) || (tc && !rho))
+        return fail(h, DFCHEM_EINVAL, std::string(who) + ": bad argument");
     if (nC == 0 || h->mech.R == 0) return DFCHEM_OK;
     CUDA_TRY(h, cudaSetDevice(h->device));
     const int N = h->mech.N, R = h->mech.R;
     const size_t ld = (size_t)nC, nb = ld * sizeof(double);
-    CUDA_TRY(h, h->scratch.ensure(((size_t)N + R + 2) * nb));
+    CUDA_TRY(h, h->scratch.ensure(((size_t)N + 3 * (size_t)R + 4) * nb));
     double* d = static_cast<double*>(h->scratch.p);
-    double *dT = d, *dp = d + ld, *dY = d + 2 * ld, *dQ = dY + (size_t)N * ld;
+    double *dT = d, *dp = d + ld, *drho = d + 2 * ld, *dtc = d + 3 * ld, *dY = d + 4 * ld, *dQ = dY + (size_t)N * ld,
+           *dQf = dQ + (size_t)R * ld, *dQr = dQf + (size_t)R * ld;
     cudaStream_t s = h->streams[0];
     CUDA_TRY(h, cudaMemcpyAsync(dT, T, nb, cudaMemcpyHostToDevice, s));
     CUDA_TRY(h, cudaMemcpyAsync(dp, p, nb, cudaMemcpyHostToDevice, s));
+    if (rho) CUDA_TRY(h, cudaMemcpyAsync(drho, rho, nb, cudaMemcpyHostToDevice, s));
     CUDA_TRY(h, cudaMemcpy2DAsync(dY, nb, Y, (size_t)ldY * sizeof(double), nb, N, cudaMemcpyHostToDevice, s));
-    int rc = dfchem_rop_dev(h, nC, dT, dp, dY, nC, dQ, nC, s);
-    if (rc != DFCHEM_OK) return rc;
-    CUDA_TRY(h, cudaMemcpy2DAsync(q, (size_t)ldQ * sizeof(double), dQ, nb, nb, R, cudaMemcpyDeviceToHost, s));
+    int rc = rop_dev_impl(h, who, nC, dT, dp, dY, nC, q ? dQ : nullptr, qf ? dQf : nullptr, qr ? dQr : nullptr, nC,
+                          rho ? drho : nullptr, tc ? dtc : nullptr, s);
+    if (rc == DFCHEM_OK) {
+        if (q) CUDA_TRY(h, cudaMemcpy2DAsync(q, (size_t)ldQ * sizeof(double), dQ, nb, nb, R, cudaMemcpyDeviceToHost, s));
+        if (qf) CUDA_TRY(h, cudaMemcpy2DAsync(qf, (size_t)ldQ * sizeof(double), dQf, nb, nb, R, cudaMemcpyDeviceToHost, s));
+        if (qr) CUDA_TRY(h, cudaMemcpy2DAsync(qr, (size_t)ldQ * sizeof(double), dQr, nb, nb, R, cudaMemcpyDeviceToHost, s));
+        if (tc) CUDA_TRY(h, cudaMemcpyAsync(tc, dtc, nb, cudaMemcpyDeviceToHost, s));
+    }
     CUDA_TRY(h, cudaStreamSynchronize(s));
-    return DFCHEM_OK;
+    return rc;
+}
+}  // namespace
+
+int dfchem_rop_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* Y, int ldY,
+                   double* q, int ldQ, void* stream) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC > 0 && !q) return fail(h, DFCHEM_EINVAL, "dfchem_rop_dev: bad argument");
+    return rop_dev_impl(h, "dfchem_rop_dev", nC, T, p, Y, ldY, q, nullptr, nullptr, ldQ, nullptr, nullptr,
+                        static_cast<cudaStream_t>(stream));
+}
+int dfchem_rop(dfchem_handle h, int nC, const double* T, const double* p, const double* Y, int ldY,
+               double* q, int ldQ) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC > 0 && !q) return fail(h, DFCHEM_EINVAL, "dfchem_rop: bad argument");
+    return rop_host_impl(h, "dfchem_rop", nC, T, p, nullptr, Y, ldY, q, nullptr, nullptr, ldQ, nullptr);
+}
+int dfchem_rop_fwd_rev_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* Y, int ldY,
+                           double* qf, double* qr, int ldQ, void* stream) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC > 0 && (!qf || !qr)) return fail(h, DFCHEM_EINVAL, "dfchem_rop_fwd_rev_dev: bad argument");
+    return rop_dev_impl(h, "dfchem_rop_fwd_rev_dev", nC, T, p, Y, ldY, nullptr, qf, qr, ldQ, nullptr, nullptr,
+                        static_cast<cudaStream_t>(stream));
+}
+int dfchem_rop_fwd_rev(dfchem_handle h, int nC, const double* T, const double* p, const double* Y, int ldY,
+                       double* qf, double* qr, int ldQ) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC > 0 && (!qf || !qr)) return fail(h, DFCHEM_EINVAL, "dfchem_rop_fwd_rev: bad argument");
+    return rop_host_impl(h, "dfchem_rop_fwd_rev", nC, T, p, nullptr, Y, ldY, nullptr, qf, qr, ldQ, nullptr);
+}
+int dfchem_tc_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* rho, const double* Y,
+                  int ldY, double* tc, void* stream) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC > 0 && (!tc || !rho)) return fail(h, DFCHEM_EINVAL, "dfchem_tc_dev: bad argument");
+    return rop_dev_impl(h, "dfchem_tc_dev", nC, T, p, Y, ldY, nullptr, nullptr, nullptr, nC, rho, tc,
+                        static_cast<cudaStream_t>(stream));
+}
+int dfchem_tc(dfchem_handle h, int nC, const double* T, const double* p, const double* rho, const double* Y, int ldY,
+              double* tc) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC > 0 && (!tc || !rho)) return fail(h, DFCHEM_EINVAL, "dfchem_tc: bad argument");
+    return rop_host_impl(h, "dfchem_tc", nC, T, p, rho, Y, ldY, nullptr, nullptr, nullptr, nC, tc);
 }
 
 int dfchem_reaction_stoich(dfchem_handle h, int reaction, double* nu_net) {
@@ -549,8 +772,12 @@ int dfchem_set_transport_fits(dfchem_handle h, const double* visc, const double*
     h->tt.cond = base + (tc - tW);
     h->tt.wilke = base + (tk - tW);
     h->tt.diff = base + (td - tW);
-    CUDA_TRY(h, cudaFuncSetAttribute(transport_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)transport_smem_bytes(N)));
+    // per-function attribute shared by every handle: always the device maximum, never this handle's size
+    int max_optin = 0;
+    CUDA_TRY(h, cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+    if (transport_smem_bytes(N) > (size_t)max_optin)
+        return fail(h, DFCHEM_EUNSUPPORTED, "transport kernel: species columns exceed the shared memory of one CTA");
+    CUDA_TRY(h, cudaFuncSetAttribute(transport_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin));
     return DFCHEM_OK;
 }
 

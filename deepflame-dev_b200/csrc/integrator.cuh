@@ -366,15 +366,20 @@ constexpr double kFacUnstable = 0.25;  // step cut when the unstable-mode guard 
 // concentration units: sc_k = atol*rho/W_k + rtol*max(|c_k|, |c_k,new|); WRMS norm over the N
 // species (CVODE's norm also counts the reactor's three constant unknowns).
 template <int NP, int NSLOT>
+// h_io (deltaTChem): a positive value on entry is the first trial step (warm start from the previous flow
+// step: the reference carries a field of that name, dfChemistryModel.H, but never feeds it to CVODE); on
+// exit it holds the step the controller would take next, ignoring the truncation at the end of the interval.
 DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT>* regs, int dfc_lane,
-                                double dt, double rtol, double atol_rho, int max_steps) {
+                                double dt, double rtol, double atol_rho, int max_steps, double& h_io) {
     (void)dfc_lane;
     StepStats st{0, 0, kCellOk};
+    const bool warm = h_io > 0.0;
+    double h_free = dt;  // last step-size proposal that was not cut by the end of the interval
     double* c = sm + m.off_c;
     double* cs = sm + m.off_cs;
     double* vec = sm + m.off_vec;
     const int NA = m.NA;
-    double t = 0.0, h = dt;
+    double t = 0.0, h = warm ? fmin(h_io, dt) : dt;
     bool after_reject = false;
     // absolute tolerance in concentration units, once per cell (not a global load + divide per attempt)
     DFC_LANES_BEGIN
@@ -394,7 +399,7 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
             DFC_LR.f0[s] = row < NA ? vec[row] : 0.0;
         }
         DFC_LANES_END
-        if (st.accepted + st.rejected == 0) {
+        if (st.accepted + st.rejected == 0 && !warm) {
             // first step size from the scaled rate norm (Hairer & Wanner II.4): h0 = K / ||f0 / sc||
             DFC_LANES_BEGIN
             double e2 = 0.0;
@@ -429,6 +434,7 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
                 st.status = kCellUnderflow;
                 return st;
             }
+            const bool cut = hs < h;
             const double ih = 1.0 / hs;
             invert_matrix<NP, NSLOT>(m, sm, regs, dfc_lane, ih / kGamma);
             // Unstable-mode guard.  det(I/(h g) - J) = product of the pivots is negative iff an odd number of
@@ -513,9 +519,13 @@ DFC_HD StepStats integrate_cell(const DevMech& m, double* sm, LaneRegs<NP, NSLOT
                 ++st.rejected;
                 after_reject = true;
             }
+            h_free = (accepted && cut) ? fmax(h, hs * fac) : hs * fac;
             h = hs * fac;
         }
-        if (t >= dt * (1.0 - 1e-14)) return st;
+        if (t >= dt * (1.0 - 1e-14)) {
+            h_io = h_free;
+            return st;
+        }
     }
 }
 

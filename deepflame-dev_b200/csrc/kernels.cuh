@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include "cell_driver.cuh"
+#include "lane_cell.cuh"
 
 namespace dfchem {
 
@@ -62,6 +63,67 @@ solve_kernel(const DevMech mg, const SolveArgs a, unsigned int* queue, unsigned 
     }
 }
 
+// ---- lane-per-cell solve kernel (small mechanisms: NA <= kLpcMaxActive) -------------------------
+// Persistent CTA per SM; every LANE owns one cell from load to RR/Qdot (lane_cell.cuh).  A warp runs one
+// step attempt per loop iteration for its 32 cells; lanes whose cell has finished go idle and are refilled
+// from the global queue in groups (kLpcRefill idle lanes at a time, one warp-aggregated atomic), so the
+// per-cell set-up (Arrhenius / equilibrium exponentials) is paid by many lanes at once and stiff cells
+// never hold back more than their own lane.
+constexpr int kLpcRefill = 8;
+__global__ void __launch_bounds__(512, 1)
+lpc_solve_kernel(const LpcMech mg, const SolveArgs a, unsigned int* queue, unsigned long long* counters) {
+    extern __shared__ double2 dfc_smem[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>(dfc_smem);
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(mg.base);
+        uint4* dst = reinterpret_cast<uint4*>(smem);
+        for (int i = threadIdx.x; i < mg.bytes / 16; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    const LpcMech m = lpc_rebase(mg, smem);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double* L = reinterpret_cast<double*>(smem + m.bytes) + (size_t)warp * m.lane_doubles * kLpcLanes + lane;
+    LpcState S;
+    S.cell = -1;
+    bool exhausted = false;
+    unsigned long long acc = 0, rej = 0, bad = 0;
+    while (true) {
+        const unsigned idle = __ballot_sync(0xffffffffu, S.cell < 0);
+        const int nidle = __popc(idle);
+        if (!exhausted && nidle >= kLpcRefill) {
+            unsigned base = 0;
+            if (lane == 0) base = atomicAdd(queue, (unsigned)nidle);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base + (unsigned)nidle >= (unsigned)a.nC) exhausted = true;  // this fetch reached the end of the batch
+            if (S.cell < 0) {
+                const unsigned my = base + (unsigned)__popc(idle & ((1u << lane) - 1u));
+                if (my < (unsigned)a.nC) lpc_begin_cell(m, L, a, (int)my, S);
+            }
+        }
+        if (__all_sync(0xffffffffu, S.cell < 0)) {
+            if (exhausted) break;
+            continue;
+        }
+        if (S.cell >= 0 && lpc_attempt(m, L, S, a.rtol, a.atol, a.max_steps)) {
+            lpc_finish_cell(m, L, a, S);
+            acc += S.acc;
+            rej += S.rej;
+            bad += S.status != kCellOk;
+            S.cell = -1;
+        }
+    }
+    for (int d = 16; d >= 1; d >>= 1) {
+        acc += __shfl_xor_sync(0xffffffffu, acc, d);
+        rej += __shfl_xor_sync(0xffffffffu, rej, d);
+        bad += __shfl_xor_sync(0xffffffffu, bad, d);
+    }
+    if (lane == 0) {
+        atomicAdd(counters + 0, acc);
+        atomicAdd(counters + 1, rej);
+        atomicAdd(counters + 2, bad);
+    }
+}
+
 template <int NP, int NSLOT>
 __global__ void __launch_bounds__(max_warps(NP) * kTeam, 1)
 wdot_kernel(const DevMech mg, int nC, const double* T, const double* p, const double* Y, int ldY,
@@ -86,7 +148,8 @@ wdot_kernel(const DevMech mg, int nC, const double* T, const double* p, const do
 template <int NP, int NSLOT>
 __global__ void __launch_bounds__(max_warps(NP) * kTeam, 1)
 rop_kernel(const DevMech mg, int nC, const double* T, const double* p, const double* Y, int ldY,
-           const int* rorder, double* q, int ldQ, unsigned int* queue) {
+           const int* rorder, double* q, double* qf, double* qr, int ldQ, const double* rxnu, const double* rho,
+           double* tc, unsigned int* queue) {
     extern __shared__ double2 dfc_smem[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(dfc_smem);
     const DevMech m = stage_hot_tables(mg, smem);
@@ -100,7 +163,7 @@ rop_kernel(const DevMech mg, int nC, const double* T, const double* p, const dou
         if (lane == 0) cell = (int)atomicAdd(queue, 1u);
         cell = __shfl_sync(0xffffffffu, cell, 0);
         if (cell >= nC) break;
-        rop_one_cell<NP, NSLOT>(m, sm, &regs, lane, T, p, Y, ldY, rorder, q, ldQ, cell);
+        rop_one_cell<NP, NSLOT>(m, sm, &regs, lane, T, p, Y, ldY, rorder, q, qf, qr, ldQ, rxnu, rho, tc, cell);
     }
 }
 

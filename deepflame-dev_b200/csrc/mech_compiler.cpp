@@ -323,6 +323,8 @@ Mechanism compile(const yaml::Node& doc) {
                 m.troe[(size_t)i * 4 + 1] = t.at("T3").as_double();
                 m.troe[(size_t)i * 4 + 2] = t.at("T1").as_double();
                 m.troe[(size_t)i * 4 + 3] = t.has("T2") ? t.at("T2").as_double() : std::numeric_limits<double>::infinity();
+                // Cantera 2.6 (TroeRate::setFalloffCoeffs): T2 = 0 means "no exp(-T2/T) term", not exp(0) = 1
+                if (m.troe[(size_t)i * 4 + 3] == 0.0) m.troe[(size_t)i * 4 + 3] = std::numeric_limits<double>::infinity();
             }
         } else if (typ == "three-body") {
             if (!e.has_m) throw std::runtime_error("mechanism: three-body reaction without M: " + m.equations[i]);

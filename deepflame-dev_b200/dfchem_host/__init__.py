@@ -17,7 +17,7 @@ from ctypes import POINTER, c_char_p, c_double, c_int, c_size_t, c_ulonglong, c_
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.environ.get("DFCHEM_LIB") or os.path.join(os.path.dirname(_HERE), "libdfchem_b200.so")  # DFCHEM_LIB: experiment builds
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libdfchem_b200.so")   # the in-tree build, nothing else
 GREAT = 1.0e15  # OpenFOAM's `great` (double precision), returned by updateReactionRates (.C:871,894)
 
 _dp = POINTER(c_double)
@@ -40,6 +40,13 @@ SIGNATURES = {
                              c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "dfchem_solve_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_double, c_void_p,
                                  c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "dfchem_solve_ptrs": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_double, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_void_p]),
+    "dfchem_bind_deltaTChem": (c_int, [c_void_p, c_void_p]),
+    "dfchem_rop_fwd_rev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int]),
+    "dfchem_rop_fwd_rev_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
+    "dfchem_tc": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "dfchem_tc_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "dfchem_wdot": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int]),
     "dfchem_wdot_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]),
     "dfchem_correct_thermo": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
@@ -150,6 +157,41 @@ class Handle:
                                          float(dt) if dt_arr is None else 0.0, _ptr(Y), Y.shape[1],
                                          _ptr(RR), RR.shape[1], _ptr(Qdot), _ptr(cost), _ptr(status)))
         return RR, Qdot
+
+    def solve_ptrs(self, T, p, rho, dt, Ys, RRs=None, Qdot=None, cost=None, status=None):
+        """dfchem_solve_ptrs: Ys / RRs are lists of N separately allocated 1-D arrays (the PtrList<volScalarField>
+        Y_ / RR_ of dfChemistryModel.H:105,121 as they are)."""
+        nC = T.shape[0]
+        assert len(Ys) == self.N and all(y.dtype == np.float64 and y.flags.c_contiguous and y.shape == (nC,) for y in Ys)
+        RRs = [np.empty(nC) for _ in range(self.N)] if RRs is None else RRs
+        Qdot = np.empty(nC) if Qdot is None else Qdot
+        yp = (c_void_p * self.N)(*[y.ctypes.data for y in Ys])
+        rp = (c_void_p * self.N)(*[r.ctypes.data for r in RRs])
+        dt_arr = None if np.isscalar(dt) else np.ascontiguousarray(dt, dtype=np.float64)
+        self.check(self.lib.dfchem_solve_ptrs(self.h, nC, _ptr(T), _ptr(p), _ptr(rho), _ptr(dt_arr),
+                                              float(dt) if dt_arr is None else 0.0, ctypes.cast(yp, c_void_p),
+                                              ctypes.cast(rp, c_void_p), _ptr(Qdot), _ptr(cost), _ptr(status)))
+        return RRs, Qdot
+
+    def bind_deltaTChem(self, arr):
+        """deltaTChem in/out array (host NumPy array for solve / solve_ptrs, a device address for the _dev form);
+        None unbinds.  The array must stay alive while bound."""
+        self._dtchem = arr
+        self.check(self.lib.dfchem_bind_deltaTChem(self.h, _ptr(arr)))
+
+    def rop_fwd_rev(self, T, p, Y):
+        """Forward and reverse rates of progress [R, nC] (PaSR.C:349-350)."""
+        nC = T.shape[0]
+        qf, qr = np.empty((self.R, nC)), np.empty((self.R, nC))
+        self.check(self.lib.dfchem_rop_fwd_rev(self.h, nC, _ptr(T), _ptr(p), _ptr(Y), Y.shape[1], _ptr(qf), _ptr(qr), nC))
+        return qf, qr
+
+    def tc(self, T, p, rho, Y):
+        """PaSR 'reactionRate' chemical time scale [nC] (PaSR.C:326-380)."""
+        nC = T.shape[0]
+        out = np.empty(nC)
+        self.check(self.lib.dfchem_tc(self.h, nC, _ptr(T), _ptr(p), _ptr(rho), _ptr(Y), Y.shape[1], _ptr(out)))
+        return out
 
     def wdot(self, T, p, Y):
         nC = T.shape[0]

@@ -30,6 +30,11 @@
  *                            initCoeffsfromBinaryFile, src_gpu/dfThermo.cu:361-435 (thermo_<mech>.txt)
  *   dfchem_rop[_dev], dfchem_reaction_stoich   dfChemistryModel::calculateRR,
  *                            dfChemistryModel.C:925-987 (getNetRatesOfProgress + projection)
+ *   dfchem_solve_ptrs        the same, taking PtrList<volScalarField> Y_ / RR_ as N separate arrays
+ *                            (dfChemistryModel.H:105,121) instead of getProblems' AoS repack (:784-823)
+ *   dfchem_bind_deltaTChem   volScalarField deltaTChem_ (dfChemistryModel.H; written :871, returned :894)
+ *   dfchem_rop_fwd_rev[_dev], dfchem_tc[_dev]   PaSR chemistry time scale "reactionRate",
+ *                            src/dfCombustionModels/PaSR/PaSR.C:326-385
  *   dfchem_balance_plan      LoadBalancer::getOperations (allAverage),
  *                            src/dfChemistryModel/loadBalancing/LoadBalancer.C:124-180
  *
@@ -57,7 +62,11 @@ enum {
     DFCHEM_EMECH = -2,     /* mechanism file missing / outside the supported dialect */
     DFCHEM_ECUDA = -3,     /* CUDA runtime error (no device, launch failure, ...) */
     DFCHEM_ENOMEM = -4,    /* host or device allocation failed */
-    DFCHEM_EUNSUPPORTED = -5 /* mechanism too large for the compiled kernel set */
+    DFCHEM_EUNSUPPORTED = -5, /* mechanism too large for the compiled kernel set */
+    DFCHEM_ECELLFAIL = -6    /* dfchem_solve / dfchem_solve_ptrs: the integrator failed in at least one cell (max steps
+                              * or step underflow); every output array is written, the failed cells hold the partial
+                              * result and a non-zero status.  The reference aborts here (uncaught CVODE error in
+                              * solveSingle, dfChemistryModel.C:738-780): the OpenFOAM wrapper turns it into FatalError */
 };
 
 /* per-cell status written by dfchem_solve* (ChemistrySolution has no such field; the reference
@@ -100,6 +109,22 @@ int dfchem_solve_dev(dfchem_handle h, int nC, const double* T, const double* p, 
                      const double* dt, double dt_uniform, const double* Y, int ldY,
                      double* RR, int ldRR, double* Qdot, double* cost, int* status, void* stream);
 
+/* Pointer-table form of dfchem_solve: Yptrs[i] / RRptrs[i] (i < N, host) are the N separately allocated
+ * arrays of PtrList<volScalarField> Y_ / RR_ (dfChemistryModel.H:105,121) as they are -- no repack into one
+ * block on the host; each species row is staged by its own asynchronous copy. */
+int dfchem_solve_ptrs(dfchem_handle h, int nC, const double* T, const double* p, const double* rho,
+                      const double* dt, double dt_uniform, const double* const* Yptrs,
+                      double* const* RRptrs, double* Qdot, double* cost, int* status);
+
+/* deltaTChem (dfChemistryModel.H `deltaTChem_`; the reference carries the field but never feeds it to
+ * CVODE: every cell cold-starts, dfChemistryModel.C:871,894).  Binding an array of nC doubles makes the
+ * following dfchem_solve* calls (a) start every cell whose entry is > 0 with that first trial step instead
+ * of the cold-start heuristic and (b) write back the step the controller would take next.  The pointer is
+ * interpreted like the other arrays of the call that uses it: host memory for dfchem_solve /
+ * dfchem_solve_ptrs, device memory for dfchem_solve_dev.  NULL unbinds.  The returned chemistry time step
+ * of solve() stays `great` (updateReactionRates, dfChemistryModel.C:894). */
+int dfchem_bind_deltaTChem(dfchem_handle h, double* deltaTChem);
+
 /* Instantaneous net production rates wrate_i = wdot_i*W_i [kg/m3/s] at (T, p, Y)
  * (calculateW, dfChemistryModel.C:897-923). */
 int dfchem_wdot(dfchem_handle h, int nC, const double* T, const double* p, const double* Y,
@@ -133,6 +158,20 @@ int dfchem_rop(dfchem_handle h, int nC, const double* T, const double* p, const 
 int dfchem_rop_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* Y,
                    int ldY, double* q, int ldQ, void* stream);
 int dfchem_reaction_stoich(dfchem_handle h, int reaction, double* nu_net /* [N] */);
+/* Forward and reverse rates of progress qf, qr [r*ldQ + c] (getFwdRatesOfProgress / getRevRatesOfProgress at
+ * setState_TPX(T, p, rho Y_i/W_i), src/dfCombustionModels/PaSR/PaSR.C:341-350), and the PaSR "reactionRate"
+ * chemical time scale tc [s] built from them (PaSR.C:352-378): tc = sum_r (wf_r + wr_r) / sum_r (wf_r^2 + wr_r^2)
+ * * sum_i rho Y_i / W_i, with wf_r = (sum of product nu) qf_r, wr_r = (sum of reactant nu) qr_r; vGreat = 1e300
+ * where nothing reacts.  rho = the caller's density.  (The "formationRate" scale, laminar.C:73-102, is
+ * max_i Y_i/|RR_i| of the solve() result and needs no entry point.) */
+int dfchem_rop_fwd_rev(dfchem_handle h, int nC, const double* T, const double* p, const double* Y,
+                       int ldY, double* qf, double* qr, int ldQ);
+int dfchem_rop_fwd_rev_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* Y,
+                           int ldY, double* qf, double* qr, int ldQ, void* stream);
+int dfchem_tc(dfchem_handle h, int nC, const double* T, const double* p, const double* rho,
+              const double* Y, int ldY, double* tc);
+int dfchem_tc_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* rho,
+                  const double* Y, int ldY, double* tc, void* stream);
 
 /* Transport part of correctThermo (dfChemistryModel.C:513-541): mu = Wilke mixture viscosity
  * [Pa s], alpha = lambda_mix / cp [kg/m/s], rhoD[i*ldD + c] = rho * D_i^mix [kg/m/s] (mass-flux
@@ -152,9 +191,13 @@ int dfchem_transport_dev(dfchem_handle h, int n, const double* T, const double* 
                          const double* rho, const double* cp, const double* Y, int ldY, double* mu,
                          double* alpha, double* rhoD, int ldD, int unity_lewis, void* stream);
 
-/* Counters of the last dfchem_solve or dfchem_solve_dev call, summed over its cells (the _dev
- * form must be synchronised by the caller first): [0] accepted steps, [1] rejected steps,
- * [2] cells with status != 0, [3] kernel launches issued by the last call. */
+/* Counters of the last dfchem_solve* call, summed over its cells: [0] accepted steps, [1] rejected steps,
+ * [2] cells with status != 0, [3] kernel launches issued by the last call.  After dfchem_solve_dev the
+ * caller must have synchronised the stream first; the _dev form cannot return DFCHEM_ECELLFAIL (it does not
+ * wait for the kernel), so its caller checks [2] here or the status array.
+ * Threading: a handle is single-caller (like dfChemistryModel, whose scratch members are not re-entrant);
+ * its _dev entry points may be issued on several streams -- every launch owns a private work-queue word and
+ * counter record -- but the counters reported here are those of the most recent solve call only. */
 int dfchem_last_counters(dfchem_handle h, unsigned long long out[4]);
 
 /* Load-balancer plan, restating LoadBalancer::getOperations (allAverage rule,

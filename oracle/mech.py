@@ -229,7 +229,7 @@ def load_mechanism(path) -> Mechanism:
             if "Troe" in r:
                 t = r["Troe"]
                 troe[i] = [float(t["A"]), float(t["T3"]), float(t["T1"]),
-                           float(t["T2"]) if "T2" in t else np.inf]
+                           float(t["T2"]) if "T2" in t and float(t["T2"]) != 0.0 else np.inf]   # Cantera 2.6: T2 = 0 means "term absent"
         elif typ == "three-body":
             assert has_m
             kind[i] = THREE_BODY

@@ -12,6 +12,7 @@
 
 #define DFC_EMU_BOUNDS 1
 #include "../../deepflame-dev_b200/csrc/cell_driver.cuh"
+#include "../../deepflame-dev_b200/csrc/lane_cell.cuh"
 #include "../../deepflame-dev_b200/csrc/dispatch.hpp"
 
 using namespace dfchem;
@@ -35,6 +36,7 @@ struct Window {
     ~Window() { dfc_emu_window = {nullptr, nullptr, nullptr}; }
 };
 struct Emu {
+    Mechanism mech;
     HostTables ht;
     DevMech dm;
 };
@@ -105,8 +107,8 @@ extern "C" {
 void* emu_create(const void* blob, size_t len) {
     try {
         Emu* e = new Emu;
-        Mechanism mech = Mechanism::deserialize(static_cast<const uint8_t*>(blob), len);
-        e->ht = build_tables(mech);
+        e->mech = Mechanism::deserialize(static_cast<const uint8_t*>(blob), len);
+        e->ht = build_tables(e->mech);
         e->dm = e->ht.rebase(e->ht.blob.data());
         return e;
     } catch (const std::exception&) {
@@ -156,6 +158,31 @@ int emu_solve(void* h, int nC, const double* T, const double* p, const double* r
         return -1;
     }
 #undef CALL
+    return 0;
+}
+// lane-per-cell path (lane_cell.cuh) run one cell after another with lane stride 1; -2: mechanism not eligible
+int emu_solve_lpc(void* h, int nC, const double* T, const double* p, const double* rho, const double* dt,
+                  double dt_uniform, const double* Y, int ldY, double* RR, int ldRR, double* Qdot,
+                  double* cost, int* status, double rtol, double atol, int max_steps,
+                  unsigned long long* counters) {
+    const Emu* e = static_cast<Emu*>(h);
+    HostLpc lpc = build_lpc_tables(e->mech, e->ht.perm, e->dm.NA);
+    if (!lpc.usable) return -2;
+    const LpcMech m = lpc.rebase(lpc.blob.data());
+    SolveArgs a{nC, T, p, rho, dt, dt_uniform, Y, ldY, RR, ldRR, Qdot, cost, status, rtol, atol, max_steps};
+    counters[0] = counters[1] = counters[2] = 0;
+    std::vector<double> L(m.lane_doubles);
+    for (int cell = 0; cell < nC; ++cell) {
+        std::fill(L.begin(), L.end(), std::numeric_limits<double>::quiet_NaN());
+        LpcState S;
+        lpc_begin_cell(m, L.data(), a, cell, S);
+        while (!lpc_attempt(m, L.data(), S, rtol, atol, max_steps)) {
+        }
+        lpc_finish_cell(m, L.data(), a, S);
+        counters[0] += S.acc;
+        counters[1] += S.rej;
+        counters[2] += S.status != 0;
+    }
     return 0;
 }
 int emu_wdot(void* h, int nC, const double* T, const double* p, const double* Y, int ldY, double* wr,

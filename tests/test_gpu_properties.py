@@ -48,7 +48,7 @@ def test_conservation_and_determinism_at_scale(api, name, n):
     assert cost.min() >= 1 and cost.max() < 5000
     # nothing happens in cold fuel/air cells (no radicals: the unburnt half of the batch): one step
     cold = (b["T"] < 500.0) & ((b["Y"] > 0).sum(0) <= 4)
-    assert cold.sum() > 0 and (cost[cold] <= 2).all()
+    assert cold.sum() > 0 and (cost[cold] <= 4).all()      # h0 = 10/||f0/sc||, growth x6: a handful of steps at most
     RR2, Q2 = h.solve(b["T"], b["p"], b["rho"], 1e-6, b["Y"])
     assert np.array_equal(RR, RR2) and np.array_equal(Q, Q2)
     # RR is linear in the caller's density (it only scales the result, dfChemistryModel.C:770)
