@@ -95,7 +95,24 @@ class ClockSampler:
 
 
 def load_oracle_c():
-    lib = ctypes.CDLL(os.path.join(ROOT, "oracle", "c", "liboracle_c.so"))
+    """The CPU arm is built where it runs, with -O3 -march=native (oracle/c/Makefile target `native`): the portable
+    liboracle_c.so that travels with the snapshot is only the fall-back when no compiler is on the box."""
+    path = os.path.join(ROOT, "oracle", "c", "liboracle_c.so")
+    native = False
+    try:
+        import hashlib
+
+        flags = next((ln for ln in open("/proc/cpuinfo") if ln.startswith("flags")), "")
+        tag = hashlib.sha1(flags.encode()).hexdigest()[:10]          # one build per distinct CPU feature set
+        subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle", "c"), "native", f"TAG={tag}"], check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=120)
+        cand = os.path.join(ROOT, "oracle", "c", f"liboracle_c_native_{tag}.so")
+        if os.path.exists(cand):
+            path, native = cand, True
+    except (OSError, subprocess.SubprocessError):
+        pass
+    lib = ctypes.CDLL(path)
+    lib.built_native = native
     lib.oc_load.restype = ctypes.c_void_p
     lib.oc_load.argtypes = [ctypes.c_char_p, ctypes.c_size_t]
     return lib
@@ -150,17 +167,19 @@ def run_reference(args, rank):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args, args.cells),   # same workload; each step times a bounded sample of it
+        "config": workload_config(args, args.cells, impl="reference"),   # same workload; each step times a bounded sample of it
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
 
 
-def workload_config(args, cells):
+def workload_config(args, cells, impl="ours"):
+    integ = ("RODAS4 (Rosenbrock 4(3), 6 stages, analytic Jacobian)" if impl == "ours" else
+             "variable-order BDF 1-5 + Newton + dense LU + finite-difference Jacobian (oracle/c, CVODE-equivalent port)")
     return {"workload": f"{args.mech} ({'mechanisms/CH4/gri30.yaml, 36 species / 219 reactions' if args.mech == 'gri30' else args.mech}), "
                         f"{cells} synthetic cells per GPU, T~U[300,2500] K, p~U[1,10] atm, 50% fuel/air phi~U[0.5,2] + 50% "
                         f"ignition-trajectory states, deltaT={args.dt:g} s",
-            "cells_per_gpu": cells, "rtol": args.rtol, "atol": args.atol, "integrator": "RODAS4 (Rosenbrock 4(3), 6 stages)",
+            "cells_per_gpu": cells, "rtol": args.rtol, "atol": args.atol, "integrator": integ,
             "l2": "inputs (T,p,rho,Y = 1.3 GB at 4M cells) exceed the 126 MB L2; no explicit flush"}
 
 

@@ -90,7 +90,10 @@ def load_library(path: str = LIB_PATH):
 
 
 class DfchemError(RuntimeError):
-    pass
+    code = 0   # the DFCHEM_E* value
+
+
+ECELLFAIL = -6  # DFCHEM_ECELLFAIL
 
 
 def _ptr(a):
@@ -125,7 +128,9 @@ class Handle:
 
     def check(self, rc):
         if rc != 0:
-            raise DfchemError(f"dfchem error {rc}: {self.lib.dfchem_last_error(self.h).decode()}")
+            err = DfchemError(f"dfchem error {rc}: {self.lib.dfchem_last_error(self.h).decode()}")
+            err.code = rc
+            raise err
 
     def close(self):
         if getattr(self, "h", None):

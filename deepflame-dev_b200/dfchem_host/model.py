@@ -17,7 +17,7 @@ from __future__ import annotations
 
 import numpy as np
 
-from . import GREAT, Handle
+from . import ECELLFAIL, GREAT, DfchemError, Handle
 
 
 class DfChemistryModel:
@@ -90,8 +90,12 @@ class DfChemistryModel:
         if not self.chemistry_:
             result = GREAT
         else:
-            self._h.solve(self.T, self.p, self.rho, float(deltaT) if scalar else deltaT, self._Y,
-                          RR=self._RR, Qdot=self._Qdot, cost=self.cpuTimes_, status=self.cellStatus_)
+            try:
+                self._h.solve(self.T, self.p, self.rho, float(deltaT) if scalar else deltaT, self._Y,
+                              RR=self._RR, Qdot=self._Qdot, cost=self.cpuTimes_, status=self.cellStatus_)
+            except DfchemError as e:
+                if e.code != ECELLFAIL:     # DFCHEM_ECELLFAIL: outputs and cellStatus_ are written, handled below
+                    raise
             if (self.cellStatus_ != 0).any():
                 bad = int(np.count_nonzero(self.cellStatus_))
                 # the reference lets CVODE failures propagate as a fatal error

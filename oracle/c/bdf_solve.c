@@ -119,6 +119,12 @@ static int bdf_integrate(Cell* c, double* y, double tend, double rtol, double at
     memset(D, 0, sizeof(double) * 8 * n);
     for (int i = 0; i < n; ++i) { D[i] = y[i]; D[n + i] = f[i] * h_abs; }
     int order = 1, n_equal = 0, have_lu = 0, current_jac = 1, status = 0;
+    /* CVODE's Newton-matrix policy (SUNDIALS cvode.c: DGMAX 0.3, MSBP 20, THRESH 1.5): the factored matrix
+     * I - c J is kept across steps and step-size changes until c = h/alpha has drifted by more than 30 % from the
+     * value it was factored with, 20 steps have passed, or the iteration fails; the correction is scaled by
+     * 2/(1 + c/c_lu) when c != c_lu; the step size is only raised when the proposed ratio is at least 1.5. */
+    double cc_lu = 0.0;
+    long steps_since_lu = 0;
     fd_jacobian(c, y, f, scale, J, yt, ft);
     while (t < tend * (1 - 1e-14)) {
         if (*nsteps >= max_steps) { status = 1; break; }
@@ -127,7 +133,7 @@ static int bdf_integrate(Cell* c, double* y, double tend, double rtol, double at
         while (!accepted) {
             if (h_abs < 1e-14 * tend) { status = 2; goto done; }
             h = h_abs; t_new = t + h;
-            if (t_new > tend) { t_new = tend; change_D(D, order, (t_new - t) / h_abs, n); n_equal = 0; have_lu = 0; }
+            if (t_new > tend) { t_new = tend; change_D(D, order, (t_new - t) / h_abs, n); n_equal = 0; }
             h = t_new - t; h_abs = h;
             for (int i = 0; i < n; ++i) {
                 double s = 0, ps = 0;
@@ -136,14 +142,16 @@ static int bdf_integrate(Cell* c, double* y, double tend, double rtol, double at
                 ypred[i] = s; psi[i] = ps / alpha[order]; scale[i] = atol + rtol * fabs(s);
             }
             const double cc = h / alpha[order];
+            if (have_lu && (fabs(cc / cc_lu - 1.0) > 0.3 || steps_since_lu >= 20)) have_lu = 0;
             int converged = 0;
             while (!converged) {
                 if (!have_lu) {
                     for (int i = 0; i < n * n; ++i) LU[i] = -cc * J[i];
                     for (int i = 0; i < n; ++i) LU[i * n + i] += 1.0;
                     if (lu_factor(LU, piv, n) != 0) { break; }
-                    have_lu = 1; ++*nlu;
+                    have_lu = 1; ++*nlu; cc_lu = cc; steps_since_lu = 0;
                 }
+                const double crate_scale = 2.0 / (1.0 + cc / cc_lu);
                 /* simplified Newton */
                 memset(d, 0, sizeof(double) * n);
                 memcpy(ynew, ypred, sizeof(double) * n);
@@ -155,6 +163,7 @@ static int bdf_integrate(Cell* c, double* y, double tend, double rtol, double at
                     ++n_iter;
                     if (!finite) break;
                     lu_solve(LU, piv, n, dy);
+                    if (crate_scale != 1.0) for (int i = 0; i < n; ++i) dy[i] *= crate_scale;
                     const double dyn = rms(dy, scale, n);
                     double rate = -1;
                     if (dy_old >= 0) {
@@ -166,6 +175,7 @@ static int bdf_integrate(Cell* c, double* y, double tend, double rtol, double at
                     dy_old = dyn;
                 }
                 if (!converged) {
+                    if (have_lu && cc_lu != cc) { have_lu = 0; continue; }   /* stale matrix: refactor at the current c first */
                     if (current_jac) break;
                     rhs(c, ypred, ft);
                     fd_jacobian(c, ypred, ft, scale, J, yt, f1);
@@ -181,7 +191,7 @@ static int bdf_integrate(Cell* c, double* y, double tend, double rtol, double at
                 h_abs *= factor; change_D(D, order, factor, n); n_equal = 0;
             } else accepted = 1;
         }
-        ++*nsteps; ++n_equal;
+        ++*nsteps; ++n_equal; ++steps_since_lu;
         t = t_new; current_jac = 0;
         memcpy(y, ynew, sizeof(double) * n);
         for (int i = 0; i < n; ++i) { D[(order + 2) * n + i] = d[i] - D[(order + 1) * n + i]; D[(order + 1) * n + i] = d[i]; }
@@ -196,8 +206,10 @@ static int bdf_integrate(Cell* c, double* y, double tend, double rtol, double at
         if (fm > best) { best = fm; delta = -1; }
         if (fp > best) { best = fp; delta = 1; }
         order += delta;
-        const double factor = fmin(10.0, safety * best);
-        h_abs *= factor; change_D(D, order, factor, n); n_equal = 0; have_lu = 0;
+        double factor = fmin(10.0, safety * best);
+        if (factor < 1.5 && delta == 0) continue;   /* THRESH: keep h (and the matrix) unless the gain is worth it */
+        if (factor < 1.5) factor = 1.0;
+        h_abs *= factor; if (factor != 1.0) change_D(D, order, factor, n); n_equal = 0;
     }
 done:
     free(buf); free(piv);

@@ -1,0 +1,118 @@
+"""Equal-tolerance accuracy: at the tolerances the benchmark is timed at (rtol 1e-6 / atol 1e-10) and at the code
+default (1e-9 / 1e-15) the device integrator must be at least as close to the converged solution as the
+CVODE-equivalent BDF port of the reference's CPU path (oracle/c) on the same cells -- maximum and 99th percentile of
+both error measures of tests/parity_common.py, per mechanism, on the 256-cell golden sets (stratified in T, p and
+progress, with negative-Y / zero-radical / X_i -> 1 / un-normalised / odd-dt edge cells).
+
+CPU form: the kernel emulation (tests/emu, the very device source) on every fourth cell.  GPU form: the library on all
+256 cells, plus the tight-tolerance RR gate on all of them and the tolerance sweep written to gpurun_out/."""
+import ctypes
+import json
+import os
+
+import numpy as np
+import pytest
+from conftest import ROOT, rr_parity_error
+from parity_common import TOLS, golden256, port_solve, stats, subset
+
+MECHS = ["es80", "h2_li", "c7_onestep", "drm19", "gri30", "ethanol66"]
+P = ctypes.POINTER(ctypes.c_double)
+
+
+def assert_no_worse(dev, port, name, tol):
+    for key in ("tol_units_max", "tol_units_p99", "parity_max", "parity_p99"):
+        # (a result already below 1 -- inside the tolerance / the parity gate -- needs no comparison)
+        assert dev[key] <= max(port[key], 1.0), (name, tol, key, dev, port)
+
+
+@pytest.fixture(scope="module")
+def emu(built):
+    lib = ctypes.CDLL(built.EMU)
+    lib.emu_create.restype = ctypes.c_void_p
+    lib.emu_create.argtypes = [ctypes.c_char_p, ctypes.c_size_t]
+    return lib
+
+
+def emu_solve(lib, name, g, rtol, atol):
+    from dfchem_host import synth
+
+    blob = synth.load_blob(name)
+    h = ctypes.c_void_p(lib.emu_create(blob, len(blob)))
+    N, n = g["Y"].shape
+    RR, Q, cost = np.zeros((N, n)), np.zeros(n), np.zeros(n)
+    st = np.zeros(n, np.int32)
+    cnt = (ctypes.c_ulonglong * 4)()
+    keep = [np.ascontiguousarray(g[k], dtype=np.float64) for k in ("T", "p", "rho", "dt", "Y")]
+    rc = lib.emu_solve(h, n, *(a.ctypes.data_as(P) for a in keep[:4]), ctypes.c_double(0.0), keep[4].ctypes.data_as(P), n,
+                       RR.ctypes.data_as(P), n, Q.ctypes.data_as(P), cost.ctypes.data_as(P),
+                       st.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), ctypes.c_double(rtol), ctypes.c_double(atol), 200000, cnt)
+    lib.emu_destroy(h)
+    assert rc == 0
+    return RR, cost, st
+
+
+@pytest.mark.parametrize("name", ["es80", "c7_onestep", "drm19", "gri30"])
+def test_emulated_kernel_no_worse_than_cvode_port(emu, name):
+    g = golden256(name)
+    g = subset(g, np.arange(0, g["T"].shape[0], 4))
+    rtol, atol = TOLS[0]                       # the benchmark's tolerances; the GPU test also covers 1e-9 / 1e-15
+    RR, cost, st = emu_solve(emu, name, g, rtol, atol)
+    assert (st == 0).all()
+    RRp, _, stp = port_solve(name, g, rtol, atol)
+    assert_no_worse(stats(RR, g, rtol, atol), stats(RRp, g, rtol, atol), name, (rtol, atol))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", MECHS)
+def test_gpu_no_worse_than_cvode_port(built, name):
+    import dfchem_host
+    from dfchem_host import synth
+
+    g = golden256(name)
+    n = g["T"].shape[0]
+    h = dfchem_host.Handle(synth.load_blob(name), 0)
+    out = {}
+    for rtol, atol in TOLS:
+        h.set_tolerances(rtol, atol)
+        cost, st = np.zeros(n), np.zeros(n, np.int32)
+        RR, _ = h.solve(np.ascontiguousarray(g["T"]), np.ascontiguousarray(g["p"]), np.ascontiguousarray(g["rho"]),
+                        np.ascontiguousarray(g["dt"]), np.ascontiguousarray(g["Y"]), cost=cost, status=st)
+        assert (st == 0).all()
+        RRp, steps, stp = port_solve(name, g, rtol, atol)
+        dev, port = stats(RR, g, rtol, atol), stats(RRp, g, rtol, atol)
+        out[f"{rtol:g}/{atol:g}"] = dict(device=dev, cvode_port=port, device_attempts_per_cell=float(cost.mean()),
+                                         port_steps_per_cell=float(steps.mean()))
+        assert_no_worse(dev, port, name, (rtol, atol))
+    h.close()
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", f"equal_tolerance_{name}.json"), "w") as f:
+        json.dump(out, f, indent=1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", MECHS)
+def test_gpu_rr_gate_on_256_cells_and_tolerance_sweep(built, name):
+    """The 1e-6 RR gate (DESIGN.md 'Parity') on all 256 golden cells at the tight tolerance, and the sweep of the
+    device tolerance from the benchmark's setting down to it (profiles/r2/parity_vs_rtol.json is this output)."""
+    import dfchem_host
+    from dfchem_host import synth
+
+    g = golden256(name)
+    n = g["T"].shape[0]
+    h = dfchem_host.Handle(synth.load_blob(name), 0)
+    args = [np.ascontiguousarray(g[k]) for k in ("T", "p", "rho", "dt", "Y")]
+    sweep = []
+    for rtol, atol in [(1e-6, 1e-10), (1e-7, 1e-12), (1e-8, 1e-14), (1e-9, 1e-15), (1e-10, 1e-18), (1e-11, 1e-20)]:
+        h.set_tolerances(rtol, atol)
+        cost, st = np.zeros(n), np.zeros(n, np.int32)
+        RR, Q = h.solve(*args, cost=cost, status=st)
+        assert (st == 0).all()
+        e = rr_parity_error(RR, g["RR"], g["Y"], g["rho"], g["dt"]).max(0)
+        sweep.append(dict(rtol=rtol, atol=atol, parity_max=float(e.max()), parity_p99=float(np.percentile(e, 99)),
+                          cells_passing=int((e <= 1).sum()), attempts_per_cell=float(cost.mean())))
+    h.close()
+    with open(os.path.join(ROOT, "gpurun_out", f"parity_vs_rtol_{name}.json"), "w") as f:
+        json.dump(sweep, f, indent=1)
+    assert sweep[-1]["parity_max"] <= 1.0, (name, sweep[-1])
+    # errors shrink with the tolerance (allowing the floor once the gate is passed)
+    assert all(b["parity_max"] <= max(a["parity_max"], 1.0) for a, b in zip(sweep, sweep[1:])), sweep
