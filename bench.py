@@ -201,7 +201,14 @@ def main():
     ap.add_argument("--skew", type=float, default=0.0,
                     help="make rank loads unequal: rank r draws T from [300 + skew*r*200, 2500] K (N > 1)")
     ap.add_argument("--rebalance", action="store_true",
-                    help="cost-weighted all-to-all-v of cells between ranks before each step (N > 1)")
+                    help="headline step through dfchem_solve_balanced_dev (in-library NCCL rebalancer, N > 1)")
+    ap.add_argument("--workload", default="synthetic", choices=["synthetic", "c5"],
+                    help="c5: the reference's real 262,144-cell drm19 flame field (config C5), chemistry + correctThermo back to back")
+    ap.add_argument("--no-configs", action="store_true", help="skip the other BASELINE.json configurations (configs object)")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaled, skewed, rebalanced leg (N > 1)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the accuracy statement (parity object)")
+    ap.add_argument("--strong-cells", type=int, default=4194304, help="total cells of the strong-scaled leg")
+    ap.add_argument("--balance-algorithm", default="allAverage", choices=["allAverage", "headTail"])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -227,49 +234,8 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     lib = dfchem_host.load_library()   # raises if the CUDA library is missing: no fallback
-    h = dfchem_host.Handle(synth.load_blob(args.mech), local)
-    h.set_tolerances(args.rtol, args.atol)
-    n = args.cells
-    T_range = (300.0 + args.skew * rank * 200.0, 2500.0) if args.skew else (300.0, 2500.0)
-    batch = synth.make_batch(args.mech, h.species, h.W, n, seed=12345 + rank, T_range=T_range)
-    N = h.N
-
-    # ---- device-resident arm -------------------------------------------------------------
-    d = {k: torch.from_numpy(v).to(dev) for k, v in batch.items()}
-    dRR = torch.empty((N, n), dtype=torch.float64, device=dev)
-    dQ = torch.empty(n, dtype=torch.float64, device=dev)
-    dcost = torch.empty(n, dtype=torch.float64, device=dev)
-    dstat = torch.empty(n, dtype=torch.int32, device=dev)
     stream = torch.cuda.current_stream()
-
-    def step_dev():
-        h.check(lib.dfchem_solve_dev(h.h, n, d["T"].data_ptr(), d["p"].data_ptr(), d["rho"].data_ptr(), None, args.dt,
-                                     d["Y"].data_ptr(), n, dRR.data_ptr(), n, dQ.data_ptr(), dcost.data_ptr(),
-                                     dstat.data_ptr(), stream.cuda_stream))
-
-    rb = None
-    if args.rebalance and world > 1:
-        from dfchem_host import balance
-
-        rb = balance.Rebalancer()
-        fields = torch.cat([d["T"][None], d["p"][None], d["rho"][None], d["Y"]], 0).contiguous()   # [N + 3, n]
-        step_dev()                                   # cost of the previous flow step = the balancer's input
-        torch.cuda.synchronize()
-        prev_cost = dcost.clone()
-
-        def solve_block(block):
-            nb = block.shape[1]
-            block = block.contiguous()
-            res = torch.empty((N + 2, nb), dtype=torch.float64, device=dev)
-            h.check(lib.dfchem_solve_dev(h.h, nb, block[0].data_ptr(), block[1].data_ptr(), block[2].data_ptr(), None,
-                                         args.dt, block[3].data_ptr(), nb, res.data_ptr(), nb, res[N].data_ptr(),
-                                         res[N + 1].data_ptr(), None, stream.cuda_stream))
-            return res
-
-        def step_dev():  # noqa: F811  (balanced variant replaces the plain step)
-            out, _ = balance.solve_balanced(rb, solve_block, fields, prev_cost, N + 2)
-            dRR.copy_(out[:N])
-            dQ.copy_(out[N])
+    alg = 0 if args.balance_algorithm == "allAverage" else 1
 
     def barrier():
         torch.cuda.synchronize()
@@ -283,6 +249,95 @@ def main():
         t = torch.tensor([x], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    class DeviceBatch:
+        """A batch resident in HBM plus its output arrays."""
+
+        def __init__(self, h, batch):
+            self.h, self.n, self.N = h, batch["T"].shape[0], h.N
+            self.d = {k: torch.from_numpy(np.ascontiguousarray(v)).to(dev) for k, v in batch.items()}
+            self.RR = torch.empty((self.N, self.n), dtype=torch.float64, device=dev)
+            self.Q = torch.empty(self.n, dtype=torch.float64, device=dev)
+            self.cost = torch.empty(self.n, dtype=torch.float64, device=dev)
+            self.stat = torch.empty(self.n, dtype=torch.int32, device=dev)
+
+        def solve(self, dt):
+            d = self.d
+            self.h.check(lib.dfchem_solve_dev(self.h.h, self.n, d["T"].data_ptr(), d["p"].data_ptr(), d["rho"].data_ptr(), None, dt,
+                                              d["Y"].data_ptr(), self.n, self.RR.data_ptr(), self.n, self.Q.data_ptr(),
+                                              self.cost.data_ptr(), self.stat.data_ptr(), stream.cuda_stream))
+
+        def solve_balanced(self, dt, prev_cost):
+            d = self.d
+            self.h.check(lib.dfchem_solve_balanced_dev(self.h.h, self.n, d["T"].data_ptr(), d["p"].data_ptr(), d["rho"].data_ptr(),
+                                                       None, dt, d["Y"].data_ptr(), self.n, self.RR.data_ptr(), self.n,
+                                                       self.Q.data_ptr(), prev_cost.data_ptr(), self.cost.data_ptr(),
+                                                       self.stat.data_ptr(), alg, stream.cuda_stream))
+
+    def time_steps(fn, steps, warmup, sampler=None):
+        """W untimed + exactly K timed steps, barrier + synchronize on both sides, CUDA events, max over ranks."""
+        for _ in range(warmup):
+            fn()
+        barrier()
+        if sampler:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        barrier()
+        ms_local = e0.elapsed_time(e1) / steps
+        return ms_local, max_over_ranks(ms_local)
+
+    def solve_stats(h, db):
+        cnt = h.counters()
+        failed = int((db.stat != 0).sum().item())
+        assert failed == 0, f"{failed} cells failed to integrate"      # a failed cell invalidates the number
+        att = float(db.cost.mean().item())
+        # one (I/(h g) - J) factorisation per step attempt, one analytic Jacobian per accepted step (RODAS4, no reuse)
+        return {"accepted_steps": cnt["accepted"], "rejected_steps": cnt["rejected"], "mean_attempts_per_cell": att,
+                "max_attempts_per_cell": float(db.cost.max().item()), "factorisations_per_cell": att,
+                "jacobians_per_cell": cnt["accepted"] / db.n, "failed_cells": failed}, cnt
+
+    h = dfchem_host.Handle(synth.load_blob(args.mech if args.workload == "synthetic" else "drm19"), local)
+    h.set_tolerances(args.rtol, args.atol)
+    N = h.N
+
+    if args.workload == "c5":
+        out = c5_leg(args, h, lib, dev, stream, time_steps, world, torch)
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        if rank == 0:
+            print(json.dumps(out), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    n = args.cells
+    T_range = (300.0 + args.skew * rank * 200.0, 2500.0) if args.skew else (300.0, 2500.0)
+    batch = synth.make_batch(args.mech, h.species, h.W, n, seed=12345 + rank, T_range=T_range)
+    db = DeviceBatch(h, batch)
+    d, dRR, dQ, dcost, dstat = db.d, db.RR, db.Q, db.cost, db.stat
+
+    if world > 1:
+        from dfchem_host import balance
+
+        balance.init_library_comm(h, dev)
+
+    step_dev = lambda: db.solve(args.dt)   # noqa: E731
+    if args.rebalance and world > 1:
+        db.solve(args.dt)                  # cost of the previous flow step = the balancer's input
+        torch.cuda.synchronize()
+        prev_cost = dcost.clone()
+        step_dev = lambda: db.solve_balanced(args.dt, prev_cost)   # noqa: E731
 
     def thermo_leg():
     # ---- correctThermo leg (HBM-bound): T from (h, p, Y), psi, rho [+ cp, hai] ------------------
@@ -320,12 +375,11 @@ def main():
                 ms_t = (t0e.elapsed_time(t1e) - tc0.elapsed_time(tc1)) / reps   # kernel alone (copy of the guess subtracted)
                 ms_t = max_over_ranks(ms_t)
                 err = float((Tw - d["T"]).abs().max().item())
+                assert err < 1e-6, f"thermo round trip off by {err} K"
                 thermo[label] = {"cells_per_s": world * n / (ms_t * 1e-3), "ms": ms_t, "algorithmic_bytes_per_cell": nbytes,
                                  "achieved_GBps": nbytes * n / (ms_t * 1e-3) / 1e9, "max_abs_T_error_K": err}
             # ---- transport part of correctThermo (FP64-bound: N^2 pair terms per cell) -------------
-            # gri30 has no thermo_<mech>.txt in the reference: synthetic fits of Cantera's functional form
-            visc, cond, diff = synth.synthetic_transport_fits(h.W)
-            h.set_transport_fits(visc, cond, diff)
+            fits_kind = load_transport(h, args.mech, synth)
             mu, al = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(2))
 
             def step_tr():
@@ -348,7 +402,7 @@ def main():
                                        "algorithmic_flops_per_cell": flops,
                                        "achieved_TFLOPs": flops * n / (ms_t * 1e-3) / 1e12,
                                        "algorithmic_bytes_per_cell": (N + 4) * 8 + (N + 2) * 8,
-                                       "fits": "synthetic (Cantera's ln T polynomial form)",
+                                       "fits": fits_kind,
                                        "finite": bool(torch.isfinite(mu).all().item() and torch.isfinite(hai).all().item())}
             del hai
         return thermo
@@ -363,25 +417,10 @@ def main():
             dist.destroy_process_group()
         return
 
-    for _ in range(args.warmup):
-        step_dev()
-    barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for _ in range(args.steps):
-        step_dev()
-    e1.record(stream)
-    barrier()
-    ms_local = e0.elapsed_time(e1) / args.steps
-    ms = max_over_ranks(ms_local)
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms_local, ms = time_steps(step_dev, args.steps, args.warmup, sampler)
     clocks = sampler.stop() if rank == 0 else None
-    cnt = h.counters()
-    failed = int((dstat != 0).sum().item())
-    cost_mean = float(dcost.mean().item())
-    cost_max = float(dcost.max().item())
+    istats, cnt = solve_stats(h, db)
     value = world * n / (ms * 1e-3)
 
     # ---- end-to-end arm: host buffers through the C ABI, copies inside the timed region --------
@@ -405,8 +444,44 @@ def main():
     e2e = {"value": world * n / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
            "h2d_bytes_per_step": (N + 3) * n * 8, "d2h_bytes_per_step": (N + 1) * n * 8,
            "matches_device_arm": same}
+    del pin, hRR, hQ
 
     thermo = thermo_leg()
+
+    # ---- strong-scaled, skewed batch with and without the in-library rebalancer (config C3) ------
+    strong = None
+    if world > 1 and not args.no_strong:
+        strong = strong_leg(args, h, lib, dev, rank, world, DeviceBatch, time_steps, sum_over_ranks, max_over_ranks, synth, torch)
+
+    # ---- the other BASELINE.json configurations, device-timed the same way (rank 0's GPU, N = 1 semantics) ----
+    configs = None
+    if world == 1 and not args.no_configs and args.mech == "gri30":   # (N = 1 only: the driver's BENCH run)
+        del db, d, dRR, dQ, dcost, dstat
+        torch.cuda.empty_cache()
+        configs = {}
+        for name, cells in (("es80", 1 << 20), ("c7_onestep", 1 << 20), ("drm19", 1 << 20)):
+            hc = dfchem_host.Handle(synth.load_blob(name), local)
+            hc.set_tolerances(args.rtol, args.atol)
+            bc = DeviceBatch(hc, synth.make_batch(name, hc.species, hc.W, cells, seed=12345))
+            for _ in range(3):
+                bc.solve(args.dt)
+            torch.cuda.synchronize()
+            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            c0.record(stream)
+            for _ in range(3):
+                bc.solve(args.dt)
+            c1.record(stream)
+            torch.cuda.synchronize()
+            msc = c0.elapsed_time(c1) / 3
+            st_c, cnt_c = solve_stats(hc, bc)
+            fl = algorithmic_flops(name, cells, cnt_c["accepted"], cnt_c["rejected"])
+            configs[f"{name}_{cells}"] = {"value": cells / (msc * 1e-3), "unit": UNIT, "ms_per_step": msc, "cells": cells,
+                                          "mean_attempts_per_cell": st_c["mean_attempts_per_cell"],
+                                          "achieved_TFLOPs": fl / (msc * 1e-3) / 1e12}
+            del bc
+            hc.close()
+        c5 = c5_leg(args, None, lib, dev, stream, time_steps, 1, torch, local=local)
+        configs["c5_drm19_real_flame_262144"] = c5["c5"]
 
     if rank == 0:
         pk = ctypes.c_double()
@@ -426,15 +501,22 @@ def main():
                 "frac": (achieved / peak) if (achieved and peak) else None, "traffic": traffic,
                 "peak_source": "dfchem_bench_fp64_peak (DFMA microbenchmark, measured in this run; MEASURED_PEAKS.json has no FP64 entry)",
                 "kernel": "solve_kernel", "algorithmic_flops_per_launch": flops,
+                "flop_model": "SURVEY 8d with N = all species of the mechanism (36 for gri30; the kernel factorises the 34 active ones)",
                 "hbm_algorithmic_GBps": (2 * N + 6) * 8 * n / (ms_local * 1e-3) / 1e9,
                 "step_attempts_per_s": (cnt["accepted"] + cnt["rejected"]) / (ms_local * 1e-3)}
+        if configs and peak:
+            for v in configs.values():
+                if "achieved_TFLOPs" in v:
+                    v["frac_of_fp64_peak"] = v["achieved_TFLOPs"] / peak
         out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                "data": "synthetic", "config": workload_config(args, n), "clocks": clocks, "e2e": e2e,
-               "gpu_launches": args.steps * 1, "roofline": roof, "rebalance": bool(rb), "skew": args.skew,
-               "integrator_stats": {"accepted_steps": cnt["accepted"], "rejected_steps": cnt["rejected"],
-                                    "mean_attempts_per_cell": cost_mean, "max_attempts_per_cell": cost_max,
-                                    "failed_cells": failed}}
+               "gpu_launches": args.steps * 1, "roofline": roof, "rebalance": bool(args.rebalance and world > 1), "skew": args.skew,
+               "integrator_stats": istats}
+        if strong is not None:
+            out["strong"] = strong
+        if configs is not None:
+            out["configs"] = configs
         if thermo is not None:
             hbm = None
             try:
@@ -451,6 +533,8 @@ def main():
                 v["roofline"] = {"bound": "hbm", "achieved": v["achieved_GBps"], "peak": hbm, "unit": "GB/s",
                                  "frac": v["achieved_GBps"] / hbm, "peak_source": src, "kernel": "thermo_kernel"}
             out["thermo"] = thermo
+        if not args.no_parity and args.mech == "gri30":
+            out["parity"] = parity_statement(args, dfchem_host, synth, local)
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             probe = min(n, 16 * threads)
@@ -459,12 +543,173 @@ def main():
             r1, el1, bsteps = cpu_reference_rate(args.mech, batch, sample, args.rtol, args.atol, args.dt, threads)
             out["cpu_baseline"] = {"value": r1, "unit": UNIT, "cores": threads, "kind": "port",
                                    "sample": f"first {sample} cells of the same batch, {el1:.1f} s, "
-                                             f"{bsteps:.1f} BDF steps/cell (oracle/c: CVODE-equivalent BDF + FD Jacobian + dense LU)"}
+                                             f"{bsteps:.1f} BDF steps/cell (oracle/c: CVODE-equivalent BDF + FD Jacobian + dense LU, "
+                                             f"CVODE matrix-reuse policy, -O3 -march=native)"}
         sys.stdout.flush()
         os.dup2(saved_stdout, 1)
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def load_transport(h, mech, synth):
+    """Transport fits for the bench's mu/alpha/rhoD leg: the mechanism compiler's own generator when the library
+    has one (dfchem_generate_transport_fits), else synthetic fits of Cantera's functional form."""
+    lib = h.lib
+    if hasattr(lib, "dfchem_generate_transport_fits"):
+        rc = lib.dfchem_generate_transport_fits(h.h)
+        if rc == 0:
+            return "generated by the mechanism compiler from the species' Lennard-Jones data (dfchem_generate_transport_fits)"
+    visc, cond, diff = synth.synthetic_transport_fits(h.W)
+    h.set_transport_fits(visc, cond, diff)
+    return "synthetic (Cantera's ln T polynomial form)"
+
+
+def c5_leg(args, h, lib, dev, stream, time_steps, world, torch, local=0):
+    """Config C5: the real 262,144-cell drm19 flame field of examples/dfLowMachFoam/notorch/twoD_reactingTGV/CH4
+    (fixture deepflame-dev_b200/data/c5_drm19_fields.npz) through chemistry + correctThermo back to back, as shipped
+    (every cell at its chemical equilibrium) and neighbour-blended at constant enthalpy (off equilibrium)."""
+    import dfchem_host
+    from dfchem_host import synth
+
+    own = h is None
+    if own:
+        h = dfchem_host.Handle(synth.load_blob("drm19"), local)
+    h.set_tolerances(1e-6, 1e-10)     # the case's odeCoeffs (constant/CanteraTorchProperties)
+    f = np.load(os.path.join(ROOT, "deepflame-dev_b200", "data", "c5_drm19_fields.npz"))
+    n, N = f["T"].shape[0], h.N
+    dt = 1e-6
+    res = {}
+    T0 = torch.from_numpy(f["T"]).to(dev)
+    Y0 = torch.from_numpy(np.ascontiguousarray(f["Y"])).to(dev)
+    p = torch.full((n,), float(f["p"]), dtype=torch.float64, device=dev)
+    he0 = torch.empty(n, dtype=torch.float64, device=dev)
+    h.check(lib.dfchem_h_from_T_dev(h.h, n, T0.data_ptr(), Y0.data_ptr(), n, he0.data_ptr(), stream.cuda_stream))
+    for label in ("as_shipped", "neighbour_blended"):
+        if label == "as_shipped":
+            T, Y, he = T0.clone(), Y0, he0
+        else:   # blend every cell with the one 8 columns further along x (512-cell rows) at constant enthalpy
+            sh = 8
+            Y = (0.5 * (Y0.view(N, 512, 512) + torch.roll(Y0.view(N, 512, 512), -sh, dims=2))).reshape(N, n).contiguous()
+            he = (0.5 * (he0.view(512, 512) + torch.roll(he0.view(512, 512), -sh, dims=1))).reshape(n).contiguous()
+            T = (0.5 * (T0.view(512, 512) + torch.roll(T0.view(512, 512), -sh, dims=1))).reshape(n).contiguous()
+        psi, rho, cp = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(3))
+        hai = torch.empty((N, n), dtype=torch.float64, device=dev)
+        RR = torch.empty((N, n), dtype=torch.float64, device=dev)
+        Q, cost = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(2))
+        stat = torch.empty(n, dtype=torch.int32, device=dev)
+        Tw = T.clone()
+
+        def thermo():
+            h.check(lib.dfchem_correct_thermo_dev(h.h, n, he.data_ptr(), p.data_ptr(), Y.data_ptr(), n, Tw.data_ptr(), psi.data_ptr(),
+                                                  rho.data_ptr(), cp.data_ptr(), hai.data_ptr(), n, stream.cuda_stream))
+
+        def chem():
+            h.check(lib.dfchem_solve_dev(h.h, n, Tw.data_ptr(), p.data_ptr(), rho.data_ptr(), None, dt, Y.data_ptr(), n,
+                                         RR.data_ptr(), n, Q.data_ptr(), cost.data_ptr(), stat.data_ptr(), stream.cuda_stream))
+
+        thermo()                                   # consistent (T, psi, rho) for the state
+        torch.cuda.synchronize()
+
+        def step():                                # one flow step's cell-local work: chemistry, then correctThermo
+            chem()
+            thermo()
+
+        _, ms = time_steps(step, 5, 3)
+        _, ms_chem = time_steps(chem, 5, 1)
+        assert int((stat != 0).sum().item()) == 0
+        res[label] = {"cells": n, "ms_chem_plus_thermo": ms, "ms_chem": ms_chem, "chem_cells_per_s": n / (ms_chem * 1e-3),
+                      "step_cells_per_s": n / (ms * 1e-3), "mean_attempts_per_cell": float(cost.mean().item()),
+                      "max_attempts_per_cell": float(cost.max().item()),
+                      "T_range_K": [float(Tw.min().item()), float(Tw.max().item())],
+                      "max_abs_RR": float(RR.abs().max().item())}
+    out = {"c5": {"workload": "examples/dfLowMachFoam/notorch/twoD_reactingTGV/CH4/0 (drm19, 512 x 512 cells, p = 101325 Pa), "
+                              "rtol 1e-6 / atol 1e-10, deltaT 1e-6: chemistry + correctThermo (T, psi, rho, cp, hai) back to back; "
+                              "data: the reference's own field files (fixture c5_drm19_fields.npz)", **res},
+           "metric": METRIC, "unit": UNIT, "value": res["neighbour_blended"]["chem_cells_per_s"], "n_gpus": world}
+    if own:
+        h.close()
+    return out
+
+
+def strong_leg(args, h, lib, dev, rank, world, DeviceBatch, time_steps, sum_over_ranks, max_over_ranks, synth, torch):
+    """Config C3 as written: ONE batch of --strong-cells cells split over the N GPUs, flame-like skew (rank r holds
+    the cells with T in the r-th of N equal slices of [300, 2500] K, so the hot ranks carry about twice the work),
+    timed without and with the in-library rebalancer (NCCL in the timed region)."""
+    n_s = args.strong_cells // world
+    lo = 300.0 + 2200.0 * rank / world
+    b = synth.make_batch(args.mech, h.species, h.W, n_s, seed=777 + rank, T_range=(lo, lo + 2200.0 / world))
+    sb = DeviceBatch(h, b)
+    sb.solve(args.dt)
+    torch.cuda.synchronize()
+    prev_cost = sb.cost.clone()
+    ref_RR = sb.RR.clone()
+    load = float(prev_cost.sum().item())
+    loads = [0.0] * world
+    t = torch.zeros(world, dtype=torch.float64, device=dev)
+    t[rank] = load
+    import torch.distributed as dist
+    dist.all_reduce(t)
+    loads = [float(x) for x in t.tolist()]
+    _, ms_plain = time_steps(lambda: sb.solve(args.dt), 2, 1)
+    _, ms_bal = time_steps(lambda: sb.solve_balanced(args.dt, prev_cost), 2, 1)
+    torch.cuda.synchronize()
+    identical = bool(torch.equal(sb.RR, ref_RR))
+    st = (ctypes.c_double * 8)()
+    h.check(lib.dfchem_balance_stats(h.h, st))
+    sent_cells = sum_over_ranks(st[0])
+    sent_bytes = sum_over_ranks(st[2])
+    plan_ms, xchg_ms = max_over_ranks(st[3]), max_over_ranks(st[4])
+    guest_ms, own_ms, call_ms = max_over_ranks(st[5]), max_over_ranks(st[6]), max_over_ranks(st[7])
+    same_all = sum_over_ranks(1.0 if identical else 0.0) == world
+    total = n_s * world
+    del sb
+    return {"cells_total": total, "cells_per_gpu": n_s, "skew": "rank r: T ~ U[300 + 2200 r/N, 300 + 2200 (r+1)/N] K",
+            "algorithm": args.balance_algorithm, "rank_loads_step_attempts": loads,
+            "load_imbalance_max_over_mean": max(loads) / (sum(loads) / world),
+            "without_rebalance": {"value": total / (ms_plain * 1e-3), "unit": UNIT, "ms_per_step": ms_plain},
+            "with_rebalance": {"value": total / (ms_bal * 1e-3), "unit": UNIT, "ms_per_step": ms_bal},
+            "speedup": ms_plain / ms_bal, "cells_migrated_per_step": sent_cells, "bytes_moved_per_step": sent_bytes,
+            "ms_plan": plan_ms, "ms_exchange_out": xchg_ms, "ms_solve_guests": guest_ms, "ms_solve_residents": own_ms,
+            "ms_balanced_call": call_ms, "exchange_fraction_of_step": (plan_ms + xchg_ms) / ms_bal,
+            "results_bit_identical_to_unbalanced": same_all}
+
+
+def parity_statement(args, dfchem_host, synth, local):
+    """Accuracy of the timed configuration, on the committed 256-cell golden set of the mechanism (converged oracle
+    RR, tests/golden/solve256_<mech>.npz): the device at the benchmark's (rtol, atol), the CVODE-equivalent port at
+    the same tolerances, and the device tolerance at which the strict 1e-6 RR gate passes on all 256 cells."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from parity_common import golden256, port_solve, stats
+
+    g = golden256(args.mech)
+    n = g["T"].shape[0]
+    h = dfchem_host.Handle(synth.load_blob(args.mech), local)
+    h.check(h.lib.dfchem_set_max_steps(h.h, 400000))
+    arrs = [np.ascontiguousarray(g[k]) for k in ("T", "p", "rho", "dt", "Y")]
+
+    def dev(rtol, atol):
+        h.set_tolerances(rtol, atol)
+        cost = np.zeros(n)
+        RR, _ = h.solve(*arrs, cost=cost)
+        return stats(RR, g, rtol, atol), float(cost.mean())
+
+    at_bench, att = dev(args.rtol, args.atol)
+    RRp, steps, _ = port_solve(args.mech, g, args.rtol, args.atol)
+    port = stats(RRp, g, args.rtol, args.atol)
+    gate = None
+    for rtol, atol in [(1e-6, 1e-10), (1e-7, 1e-12), (1e-8, 1e-14), (1e-9, 1e-15), (1e-10, 1e-18), (1e-11, 1e-20)]:
+        st, a = dev(rtol, atol)
+        if st["parity_max"] <= 1.0:
+            gate = {"rtol": rtol, "atol": atol, "parity_max": st["parity_max"], "attempts_per_cell": a}
+            break
+    h.close()
+    return {"cells": n, "golden": f"tests/golden/solve256_{args.mech}.npz (SciPy Radau, rtol 1e-12)",
+            "measures": "per-cell maxima; tol_units = |RR - RR_conv| / (rho/dt (rtol |Y| + atol)); parity = |RR - RR_conv| / "
+                        "(1e-6 |RR_conv| + rho/dt (1e-9 |Y| + 1e-15))",
+            "err_at_bench_tol": at_bench, "attempts_per_cell_at_bench_tol": att,
+            "err_cvode_port_at_bench_tol": port, "port_steps_per_cell": float(steps.mean()),
+            "rtol_gate_passes_at": gate}
 
 
 if __name__ == "__main__":

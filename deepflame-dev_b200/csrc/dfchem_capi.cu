@@ -12,6 +12,7 @@
 #include "../../include/dfchem.h"
 #include "dispatch.hpp"
 #include "kernels.cuh"
+#include "rebalance.cuh"
 #include "transport.cuh"
 
 using namespace dfchem;
@@ -60,6 +61,16 @@ struct dfchem_ctx {
     unsigned long long call_acc[3] = {0, 0, 0};  // counters already folded on the host (calls longer than the ring)
     unsigned long long launches = 0;
     double* dtchem = nullptr;                 // dfchem_bind_deltaTChem
+    // in-library load balancer (rebalance.cuh)
+    ncclComm_t comm = nullptr;
+    bool comm_owned = false;
+    int nranks = 1, rank = 0;
+    cudaStream_t comm_stream = nullptr;
+    cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    DevBuf bal_prefix, bal_scan_tmp, bal_small, bal_guest_in, bal_guest_out;
+    int* h_counts = nullptr;                  // pinned [nranks^2]
+    double bal_stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    bool bal_timed = false;
     int* d_rxsum = nullptr;                   // not used on the host; see d_rxnu
     double* d_rxnu = nullptr;                 // [2R] internal order: sum of product / reactant stoichiometric coefficients
     int* d_rorder = nullptr;                  // [R] internal -> caller's reaction index (rop kernel)
@@ -335,6 +346,16 @@ void dfchem_destroy(dfchem_handle h) {
     if (h->d_counters) cudaFree(h->d_counters);
     if (h->d_rorder) cudaFree(h->d_rorder);
     if (h->d_lpc) cudaFree(h->d_lpc);
+    if (h->comm && h->comm_owned && nccl_api().ok()) nccl_api().CommDestroy(h->comm);
+    if (h->comm_stream) cudaStreamDestroy(h->comm_stream);
+    for (cudaEvent_t e : h->ev)
+        if (e) cudaEventDestroy(e);
+    h->bal_prefix.release();
+    h->bal_scan_tmp.release();
+    h->bal_small.release();
+    h->bal_guest_in.release();
+    h->bal_guest_out.release();
+    if (h->h_counts) cudaFreeHost(h->h_counts);
     if (h->d_rxnu) cudaFree(h->d_rxnu);
     h->d_transport.release();
     delete h;
@@ -888,31 +909,228 @@ int dfchem_bench_fp64_peak(int device, double* tflops) {
     return cudaGetLastError() == cudaSuccess && best > 0 ? DFCHEM_OK : DFCHEM_ECUDA;
 }
 
-// allAverage rule of LoadBalancer::getOperations (loadBalancing/LoadBalancer.C:124-180): sort
-// ranks by load, repeatedly pair the heaviest sender with the lightest receiver and move
-// min(sender - mean, mean - receiver); drop operations below 1 % of the mean.
-int dfchem_balance_plan(const double* loads, int n, double* send) {
-    if (!loads || !send || n < 1) return DFCHEM_EINVAL;
-    std::fill(send, send + (size_t)n * n, 0.0);
-    double mean = 0.0;
-    for (int i = 0; i < n; ++i) mean += loads[i];
-    mean /= n;
-    std::vector<int> order(n);
-    for (int i = 0; i < n; ++i) order[i] = i;
-    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return loads[a] < loads[b]; });
-    std::vector<double> v(n);
-    for (int i = 0; i < n; ++i) v[i] = loads[order[i]];
-    int lo = 0, hi = n - 1;  // lightest receiver, heaviest sender
-    while (lo < hi) {
-        const double give = v[hi] - mean, take = mean - v[lo];
-        if (!(give > 0.0) || !(take > 0.0)) break;
-        const double x = std::min(give, take);
-        if (x > 0.01 * mean) send[(size_t)order[hi] * n + order[lo]] += x;
-        v[hi] -= x;
-        v[lo] += x;
-        if (v[hi] - mean <= 1e-12 * mean) --hi;
-        if (mean - v[lo] <= 1e-12 * mean) ++lo;
+// allAverage / headTail rules of LoadBalancer::getOperations / getOperationsRedezVous
+// (loadBalancing/LoadBalancer.C:124-180, :183-232): the same code the device planner runs (rebalance.cuh).
+int dfchem_balance_plan2(const double* loads, int n, int algorithm, double* send) {
+    if (!loads || !send || n < 1 || n > kMaxRanks || algorithm < 0 || algorithm > 1) return DFCHEM_EINVAL;
+    for (int me = 0; me < n; ++me) balance_plan_row(loads, n, me, algorithm, send + (size_t)me * n);
+    return DFCHEM_OK;
+}
+int dfchem_balance_plan(const double* loads, int n, double* send) { return dfchem_balance_plan2(loads, n, 0, send); }
+// Host form of the device planner (same code): cells rank `me` sends to every rank, given all loads and its own
+// per-cell cost.  Used by the CPU tests of the N > 1 protocol; dfchem_solve_balanced_dev runs it on the device.
+int dfchem_balance_counts(const double* loads, int n, int me, int algorithm, const double* cost, int nC, int* counts_row) {
+    if (!loads || !cost || !counts_row || n < 1 || n > kMaxRanks || me < 0 || me >= n || nC < 1 || algorithm < 0 || algorithm > 1)
+        return DFCHEM_EINVAL;
+    std::vector<double> prefix((size_t)nC);
+    double acc = 0.0;
+    for (int i = 0; i < nC; ++i) prefix[i] = (acc += cost[i]);
+    double send[kMaxRanks];
+    balance_plan_row(loads, n, me, algorithm, send);
+    balance_split_row(send, n, prefix.data(), nC, counts_row);
+    return DFCHEM_OK;
+}
+
+#define NCCL_TRY(h, call)                                                                            \
+    do {                                                                                             \
+        ncclResult_t r_ = (call);                                                                    \
+        if (r_ != ncclSuccess)                                                                       \
+            return fail(h, DFCHEM_ENCCL, std::string(#call) + ": " + nccl_api().GetErrorString(r_)); \
+    } while (0)
+
+int dfchem_comm_unique_id(void* id128) {
+    if (!id128) return DFCHEM_EINVAL;
+    if (!nccl_api().ok()) return fail(nullptr, DFCHEM_ENCCL, "libnccl.so.2 not found");
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId id;
+    if (nccl_api().GetUniqueId(&id) != ncclSuccess) return fail(nullptr, DFCHEM_ENCCL, "ncclGetUniqueId failed");
+    std::memcpy(id128, &id, sizeof(id));
+    return DFCHEM_OK;
+}
+
+static int comm_common(dfchem_ctx* h) {
+    if (!h->comm_stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->comm_stream, cudaStreamNonBlocking));
+    for (cudaEvent_t& e : h->ev)
+        if (!e) CUDA_TRY(h, cudaEventCreate(&e));
+    if (!h->h_counts) CUDA_TRY(h, cudaMallocHost(&h->h_counts, sizeof(int) * (size_t)kMaxRanks * kMaxRanks));
+    return DFCHEM_OK;
+}
+
+int dfchem_comm_init(dfchem_handle h, int nranks, int rank, const void* id128) {
+    if (!h || !id128 || nranks < 1 || nranks > kMaxRanks || rank < 0 || rank >= nranks)
+        return fail(h, DFCHEM_EINVAL, "dfchem_comm_init: bad argument");
+    if (!nccl_api().ok()) return fail(h, DFCHEM_ENCCL, "libnccl.so.2 not found");
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    ncclUniqueId id;
+    std::memcpy(&id, id128, sizeof(id));
+    NCCL_TRY(h, nccl_api().CommInitRank(&h->comm, nranks, id, rank));
+    h->comm_owned = true;
+    h->nranks = nranks;
+    h->rank = rank;
+    return comm_common(h);
+}
+
+int dfchem_comm_attach(dfchem_handle h, void* nccl_comm, int nranks, int rank) {
+    if (!h || !nccl_comm || nranks < 1 || nranks > kMaxRanks || rank < 0 || rank >= nranks)
+        return fail(h, DFCHEM_EINVAL, "dfchem_comm_attach: bad argument");
+    if (!nccl_api().ok()) return fail(h, DFCHEM_ENCCL, "libnccl.so.2 not found");
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    h->comm = static_cast<ncclComm_t>(nccl_comm);
+    h->comm_owned = false;
+    h->nranks = nranks;
+    h->rank = rank;
+    return comm_common(h);
+}
+
+// One balanced chemistry sub-step (solve_CVODE with loadbalancing active, dfChemistryModel.C:1031-1082).
+int dfchem_solve_balanced_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* rho,
+                              const double* dt, double dt_uniform, const double* Y, int ldY, double* RR, int ldRR,
+                              double* Qdot, const double* cost_prev, double* cost, int* status, int algorithm,
+                              void* stream) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC < 1 || !T || !p || !rho || !Y || !RR || !Qdot || !cost || ldY < nC || ldRR < nC || algorithm < 0 || algorithm > 1)
+        return fail(h, DFCHEM_EINVAL, "dfchem_solve_balanced_dev: bad argument (nC >= 1 and a cost array are required)");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    for (double& v : h->bal_stats) v = 0.0;
+    h->bal_timed = false;
+    if (!h->comm || h->nranks == 1 || !cost_prev)   // nothing to balance against / no cost yet: the plain sub-step
+        return dfchem_solve_dev(h, nC, T, p, rho, dt, dt_uniform, Y, ldY, RR, ldRR, Qdot, cost, status, stream);
+    if (h->dtchem) return fail(h, DFCHEM_EUNSUPPORTED, "dfchem_solve_balanced_dev: unbind deltaTChem first (migrated cells carry no step history)");
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    NcclApi& nc = nccl_api();
+    const int n = h->nranks, me = h->rank, N = h->mech.N;
+    begin_solve_call(h);
+
+    // ---- plan on the device: prefix sum of the cost, all-gather of the loads, pairing + split, all-gather of counts
+    CUDA_TRY(h, cudaEventRecord(h->ev[0], s));
+    CUDA_TRY(h, h->bal_prefix.ensure((size_t)nC * sizeof(double)));
+    CUDA_TRY(h, h->bal_small.ensure(sizeof(double) * kMaxRanks + sizeof(int) * (size_t)(kMaxRanks + kMaxRanks * kMaxRanks)));
+    double* d_prefix = static_cast<double*>(h->bal_prefix.p);
+    double* d_loads = static_cast<double*>(h->bal_small.p);
+    int* d_row = reinterpret_cast<int*>(d_loads + kMaxRanks);
+    int* d_counts = d_row + kMaxRanks;
+    size_t tmp_bytes = 0;
+    CUDA_TRY(h, cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, cost_prev, d_prefix, nC, s));
+    CUDA_TRY(h, h->bal_scan_tmp.ensure(tmp_bytes));
+    CUDA_TRY(h, cub::DeviceScan::InclusiveSum(h->bal_scan_tmp.p, tmp_bytes, cost_prev, d_prefix, nC, s));
+    NCCL_TRY(h, nc.AllGather(d_prefix + (nC - 1), d_loads, 1, ncclDouble, h->comm, s));
+    plan_split_kernel<<<1, 32, 0, s>>>(d_loads, n, me, algorithm, d_prefix, nC, d_row);
+    CUDA_TRY(h, cudaGetLastError());
+    NCCL_TRY(h, nc.AllGather(d_row, d_counts, n, ncclInt, h->comm, s));
+    CUDA_TRY(h, cudaMemcpyAsync(h->h_counts, d_counts, sizeof(int) * (size_t)n * n, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(h, cudaStreamSynchronize(s));   // the one host synchronisation: cell counts size the exchanges
+    int send_cnt[kMaxRanks], recv_cnt[kMaxRanks], send_off[kMaxRanks], recv_off[kMaxRanks];
+    int n_send = 0, n_recv = 0;
+    for (int j = 0; j < n; ++j) {
+        send_cnt[j] = h->h_counts[(size_t)me * n + j];
+        recv_cnt[j] = h->h_counts[(size_t)j * n + me];
+        send_off[j] = n_send;
+        recv_off[j] = n_recv;
+        n_send += send_cnt[j];
+        n_recv += recv_cnt[j];
     }
+    if (n_send > 0 && n_recv > 0) return fail(h, DFCHEM_EINVAL, "balance plan: a rank may be sender or receiver, not both");
+    CUDA_TRY(h, cudaEventRecord(h->ev[1], s));
+
+    // ---- exchange: N + 4 row slices per peer, straight out of the caller's arrays into the guest block
+    const size_t gl = (size_t)std::max(n_recv, 1);
+    CUDA_TRY(h, h->bal_guest_in.ensure((size_t)(N + 4) * gl * sizeof(double)));
+    CUDA_TRY(h, h->bal_guest_out.ensure(((size_t)(N + 2) * gl) * sizeof(double) + gl * sizeof(int)));
+    double* gin = static_cast<double*>(h->bal_guest_in.p);     // rows T, p, rho, dt, Y[N]; leading dimension gl
+    double* gout = static_cast<double*>(h->bal_guest_out.p);   // rows RR[N], Qdot, cost; then int status[gl]
+    int* gstat = reinterpret_cast<int*>(gout + (size_t)(N + 2) * gl);
+    cudaStream_t cs = h->comm_stream;
+    CUDA_TRY(h, cudaStreamWaitEvent(cs, h->ev[1], 0));
+    CUDA_TRY(h, cudaEventRecord(h->ev[2], cs));
+    NCCL_TRY(h, nc.GroupStart());
+    for (int j = 0; j < n; ++j) {
+        if (send_cnt[j] > 0) {
+            const size_t o = (size_t)send_off[j], c = (size_t)send_cnt[j];
+            NCCL_TRY(h, nc.Send(T + o, c, ncclDouble, j, h->comm, cs));
+            NCCL_TRY(h, nc.Send(p + o, c, ncclDouble, j, h->comm, cs));
+            NCCL_TRY(h, nc.Send(rho + o, c, ncclDouble, j, h->comm, cs));
+            if (dt) NCCL_TRY(h, nc.Send(dt + o, c, ncclDouble, j, h->comm, cs));
+            for (int k = 0; k < N; ++k) NCCL_TRY(h, nc.Send(Y + (size_t)k * ldY + o, c, ncclDouble, j, h->comm, cs));
+        }
+        if (recv_cnt[j] > 0) {
+            const size_t o = (size_t)recv_off[j], c = (size_t)recv_cnt[j];
+            NCCL_TRY(h, nc.Recv(gin + o, c, ncclDouble, j, h->comm, cs));
+            NCCL_TRY(h, nc.Recv(gin + gl + o, c, ncclDouble, j, h->comm, cs));
+            NCCL_TRY(h, nc.Recv(gin + 2 * gl + o, c, ncclDouble, j, h->comm, cs));
+            if (dt) NCCL_TRY(h, nc.Recv(gin + 3 * gl + o, c, ncclDouble, j, h->comm, cs));
+            for (int k = 0; k < N; ++k) NCCL_TRY(h, nc.Recv(gin + (size_t)(4 + k) * gl + o, c, ncclDouble, j, h->comm, cs));
+        }
+    }
+    NCCL_TRY(h, nc.GroupEnd());
+    CUDA_TRY(h, cudaEventRecord(h->ev[3], cs));
+
+    // ---- guests first (their results travel home while the residents are integrated), then the residents
+    int rc = DFCHEM_OK;
+    CUDA_TRY(h, cudaStreamWaitEvent(s, h->ev[3], 0));
+    if (n_recv > 0) {
+        SolveArgs ga{n_recv, gin, gin + gl, gin + 2 * gl, dt ? gin + 3 * gl : nullptr, dt_uniform, gin + 4 * gl, (int)gl,
+                     gout, (int)gl, gout + (size_t)N * gl, gout + (size_t)(N + 1) * gl, gstat, h->rtol, h->atol, h->max_steps, nullptr};
+        rc = launch_solve(h, ga, s);
+        if (rc != DFCHEM_OK) return rc;
+    }
+    CUDA_TRY(h, cudaEventRecord(h->ev[4], s));
+    const int n_own = nC - n_send;
+    if (n_own > 0) {
+        const size_t o = (size_t)n_send;
+        SolveArgs oa{n_own, T + o, p + o, rho + o, dt ? dt + o : nullptr, dt_uniform, Y + o, ldY, RR + o, ldRR, Qdot + o,
+                     cost + o, status ? status + o : nullptr, h->rtol, h->atol, h->max_steps, nullptr};
+        rc = launch_solve(h, oa, s);
+        if (rc != DFCHEM_OK) return rc;
+    }
+    CUDA_TRY(h, cudaEventRecord(h->ev[5], s));
+
+    // ---- results return to the owner, straight into its RR / Qdot / cost / status arrays
+    CUDA_TRY(h, cudaStreamWaitEvent(cs, h->ev[4], 0));
+    NCCL_TRY(h, nc.GroupStart());
+    for (int j = 0; j < n; ++j) {
+        if (recv_cnt[j] > 0) {   // guests of rank j go home
+            const size_t o = (size_t)recv_off[j], c = (size_t)recv_cnt[j];
+            for (int k = 0; k < N; ++k) NCCL_TRY(h, nc.Send(gout + (size_t)k * gl + o, c, ncclDouble, j, h->comm, cs));
+            NCCL_TRY(h, nc.Send(gout + (size_t)N * gl + o, c, ncclDouble, j, h->comm, cs));
+            NCCL_TRY(h, nc.Send(gout + (size_t)(N + 1) * gl + o, c, ncclDouble, j, h->comm, cs));
+            NCCL_TRY(h, nc.Send(gstat + o, c, ncclInt, j, h->comm, cs));
+        }
+        if (send_cnt[j] > 0) {
+            const size_t o = (size_t)send_off[j], c = (size_t)send_cnt[j];
+            for (int k = 0; k < N; ++k) NCCL_TRY(h, nc.Recv(RR + (size_t)k * ldRR + o, c, ncclDouble, j, h->comm, cs));
+            NCCL_TRY(h, nc.Recv(Qdot + o, c, ncclDouble, j, h->comm, cs));
+            NCCL_TRY(h, nc.Recv(cost + o, c, ncclDouble, j, h->comm, cs));
+            // without a caller status array the migrated cells' status lands in the prefix-sum buffer (idle by now)
+            NCCL_TRY(h, nc.Recv(status ? status + o : reinterpret_cast<int*>(d_prefix) + o, c, ncclInt, j, h->comm, cs));
+        }
+    }
+    NCCL_TRY(h, nc.GroupEnd());
+    CUDA_TRY(h, cudaEventRecord(h->ev[6], cs));
+    CUDA_TRY(h, cudaStreamWaitEvent(s, h->ev[6], 0));
+    CUDA_TRY(h, cudaEventRecord(h->ev[7], s));
+    h->bal_stats[0] = n_send;
+    h->bal_stats[1] = n_recv;
+    h->bal_stats[2] = (double)n_send * ((N + 3 + (dt ? 1 : 0)) * 8.0) + (double)n_recv * ((N + 2) * 8.0 + 4.0);   // bytes this rank sent
+    h->bal_timed = true;
+    return DFCHEM_OK;
+}
+
+// [0] cells sent, [1] guest cells received, [2] bytes sent by this rank (both directions), then milliseconds of the
+// last balanced call: [3] plan (prefix sum, two all-gathers, pairing, count copy), [4] outbound exchange,
+// [5] guest solve, [6] resident solve, [7] whole call.  The caller must have synchronised the stream.
+int dfchem_balance_stats(dfchem_handle h, double out[8]) {
+    if (!h || !out) return DFCHEM_EINVAL;
+    if (h->bal_timed) {
+        float ms = 0.f;
+        auto el = [&](int a, int b) { return cudaEventElapsedTime(&ms, h->ev[a], h->ev[b]) == cudaSuccess ? (double)ms : -1.0; };
+        h->bal_stats[3] = el(0, 1);
+        h->bal_stats[4] = el(2, 3);
+        h->bal_stats[5] = el(1, 4);
+        h->bal_stats[6] = el(4, 5);
+        h->bal_stats[7] = el(0, 7);
+        h->bal_timed = false;
+    }
+    std::copy(h->bal_stats, h->bal_stats + 8, out);
     return DFCHEM_OK;
 }
 

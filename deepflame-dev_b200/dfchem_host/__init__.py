@@ -66,6 +66,14 @@ SIGNATURES = {
                                      c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "dfchem_last_counters": (c_int, [c_void_p, POINTER(c_ulonglong)]),
     "dfchem_balance_plan": (c_int, [_dp, c_int, _dp]),
+    "dfchem_balance_plan2": (c_int, [_dp, c_int, c_int, _dp]),
+    "dfchem_balance_counts": (c_int, [_dp, c_int, c_int, c_int, _dp, c_int, _ip]),
+    "dfchem_comm_unique_id": (c_int, [c_void_p]),
+    "dfchem_comm_init": (c_int, [c_void_p, c_int, c_int, c_void_p]),
+    "dfchem_comm_attach": (c_int, [c_void_p, c_void_p, c_int, c_int]),
+    "dfchem_solve_balanced_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_double, c_void_p,
+                                          c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "dfchem_balance_stats": (c_int, [c_void_p, _dp]),
     "dfchem_bench_fp64_peak": (c_int, [c_int, _dp]),
     "dfchem_version": (c_char_p, []),
 }

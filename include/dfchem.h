@@ -35,7 +35,9 @@
  *   dfchem_bind_deltaTChem   volScalarField deltaTChem_ (dfChemistryModel.H; written :871, returned :894)
  *   dfchem_rop_fwd_rev[_dev], dfchem_tc[_dev]   PaSR chemistry time scale "reactionRate",
  *                            src/dfCombustionModels/PaSR/PaSR.C:326-385
- *   dfchem_balance_plan      LoadBalancer::getOperations (allAverage),
+ *   dfchem_solve_balanced_dev, dfchem_comm_*   LoadBalancerBase::balance / getRemaining / unbalance,
+ *                            loadBalancing/LoadBalancerBase.H:143-255, updateState LoadBalancer.C:29-56
+ *   dfchem_balance_plan[2]   LoadBalancer::getOperations (allAverage) / getOperationsRedezVous (headTail),
  *                            src/dfChemistryModel/loadBalancing/LoadBalancer.C:124-180
  *
  * Layout: species-major SoA, element (species i, cell c) at  X[i*ld + c]  (the layout of
@@ -63,6 +65,7 @@ enum {
     DFCHEM_ECUDA = -3,     /* CUDA runtime error (no device, launch failure, ...) */
     DFCHEM_ENOMEM = -4,    /* host or device allocation failed */
     DFCHEM_EUNSUPPORTED = -5, /* mechanism too large for the compiled kernel set */
+    DFCHEM_ENCCL = -7,       /* NCCL missing or a collective failed (load balancer) */
     DFCHEM_ECELLFAIL = -6    /* dfchem_solve / dfchem_solve_ptrs: the integrator failed in at least one cell (max steps
                               * or step underflow); every output array is written, the failed cells hold the partial
                               * result and a non-zero status.  The reference aborts here (uncaught CVODE error in
@@ -205,6 +208,37 @@ int dfchem_last_counters(dfchem_handle h, unsigned long long out[4]);
  * loads[n_ranks] -> send[from*n_ranks + to] = load units to move (0 on the diagonal);
  * operations smaller than 1 % of the mean load are dropped as in the reference. */
 int dfchem_balance_plan(const double* loads, int n_ranks, double* send);
+/* The same with the pairing rule chosen: algorithm 0 = allAverage, 1 = headTail (getOperationsRedezVous,
+ * LoadBalancer.C:183-232: the i-th heaviest rank gives half its excess over the i-th lightest). */
+int dfchem_balance_plan2(const double* loads, int n_ranks, int algorithm, double* send);
+/* timesToProblemCounts (LoadBalancer.C:97-122) for rank `me`: counts_row[to] = how many leading cells of its batch
+ * (index order) go to each rank, given every rank's load and its own per-cell cost; at least one cell stays.  Host
+ * form of the planner dfchem_solve_balanced_dev runs on the device. */
+int dfchem_balance_counts(const double* loads, int n_ranks, int me, int algorithm, const double* cost, int nC,
+                          int* counts_row);
+
+/* In-library load balancer (loadBalancing/LoadBalancerBase.H:143-255 balance / getRemaining / unbalance) over NCCL:
+ * one rank per GPU, each with its own handle.  The communicator is either created here from an id that rank 0
+ * obtained with dfchem_comm_unique_id and handed to the others by whatever the caller has (MPI_Bcast in the
+ * reference's dfNcclBase, src_gpu/dfNcclBase.cu:40-56), or an existing ncclComm_t is attached. */
+int dfchem_comm_unique_id(void* id128 /* 128 bytes out */);
+int dfchem_comm_init(dfchem_handle h, int n_ranks, int rank, const void* id128);
+int dfchem_comm_attach(dfchem_handle h, void* nccl_comm, int n_ranks, int rank);
+/* Balanced chemistry sub-step, device pointers, stream-ordered except for ONE host wait on 4 n_ranks^2 bytes (the
+ * cell counts that size the exchanges).  cost_prev [nC]: the per-cell cost of the previous flow step (the `cost`
+ * output of the previous call; NULL = plain dfchem_solve_dev); cost [nC] is required.  Loads are all-gathered, the
+ * chosen rule pairs senders with receivers, a sender ships the leading cells of its batch (index order, as
+ * timesToProblemCounts walks the problem list, LoadBalancer.C:97-122) until their summed cost reaches the share,
+ * guests are integrated where they land and their RR / Qdot / cost / status return into the owner's arrays: results
+ * are bit-identical to the unbalanced call.  Collective: every rank of the communicator must call it. */
+int dfchem_solve_balanced_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* rho,
+                              const double* dt, double dt_uniform, const double* Y, int ldY, double* RR,
+                              int ldRR, double* Qdot, const double* cost_prev, double* cost, int* status,
+                              int algorithm, void* stream);
+/* Of the last balanced call (stream synchronised by the caller): [0] cells sent, [1] guest cells received,
+ * [2] bytes sent by this rank, then ms: [3] plan, [4] outbound exchange, [5] guest solve, [6] resident solve,
+ * [7] whole call. */
+int dfchem_balance_stats(dfchem_handle h, double out[8]);
 
 /* Measurement helper: FP64 DFMA throughput of `device` in TFLOP/s (16 independent chains per
  * thread, best of 4 timed launches).  It is the denominator bench.py reports "% of FP64 peak"

@@ -12,14 +12,67 @@ import torch.multiprocessing as mp
 
 
 def test_counts_follow_times_to_problem_counts(built):
+    """dfchem_balance_counts = timesToProblemCounts (LoadBalancer.C:97-122): leading cells in index order until the
+    summed cost reaches the share; at least one cell stays."""
     from dfchem_host import balance
 
-    cost = np.array([9.0, 7.0, 5.0, 3.0, 1.0, 1.0])           # already sorted, expensive first
-    # 10 units to rank A, 5 to rank B: prefix sums 9, 16 -> two cells reach >= 10; next 5 -> one cell
-    assert balance.counts_for_units(cost, np.array([10.0, 0.0, 5.0])).tolist() == [2, 0, 1]
-    # never send everything: at least one cell stays
-    assert balance.counts_for_units(cost, np.array([1e9])).tolist() == [5]
-    assert balance.counts_for_units(np.array([]), np.array([3.0])).tolist() == [0]
+    cost = np.array([9.0, 7.0, 5.0, 3.0, 1.0, 1.0])
+    # two ranks, rank 0 heavy: loads (26, 6) -> mean 16 -> rank 0 gives 10 units: cell 0 (9 <= 10); cell 1 would
+    # bring the sum to 16 > 10 and stays (count_while(sum <= time) of the reference)
+    assert balance.counts_row(np.array([26.0, 6.0]), 0, cost).tolist() == [0, 1]
+    assert balance.counts_row(np.array([42.0, 6.0]), 0, cost).tolist() == [0, 2]              # 18 units: 9 + 7 <= 18 < 21
+    assert balance.counts_row(np.array([26.0, 6.0]), 1, np.ones(6)).tolist() == [0, 0]       # the receiver sends nothing
+    # three ranks (26, 16, 3): mean 15 -> rank 0 gives 11 to rank 2 (lightest), rank 1 gives its 1 unit to rank 2 as well
+    assert balance.counts_row(np.array([26.0, 16.0, 3.0]), 0, cost).tolist() == [0, 0, 1]
+    # never send everything
+    assert balance.counts_row(np.array([1e9, 0.0]), 0, cost).sum() == 5
+    # a single cell cannot be given away
+    assert balance.counts_row(np.array([10.0, 0.0]), 0, np.array([10.0])).sum() == 0
+
+
+def _reference_pairing(loads, head_tail):
+    """LoadBalancer::getOperations / getOperationsRedezVous restated literally (LoadBalancer.C:124-232)."""
+    n = len(loads)
+    mean = float(np.mean(loads))
+    order = sorted(range(n), key=lambda i: loads[i])
+    v = [float(loads[i]) for i in order]
+    send = np.zeros((n, n))
+    if head_tail:
+        for i in range(n // 2):
+            hi, lo = n - 1 - i, i
+            x = (v[hi] - v[lo]) / 2
+            if x > 0.01 * mean:
+                send[order[hi], order[lo]] += x
+            v[hi] -= x
+            v[lo] += x
+        return send
+    hi, lo = n - 1, 0
+    while hi != lo:
+        x = min(v[hi] - mean, mean - v[lo])
+        if x > 0.01 * mean:
+            send[order[hi], order[lo]] += x
+        v[hi] -= x
+        v[lo] += x
+        if abs(v[hi] - mean) < 1e-15 * max(mean, 1.0) or v[hi] - mean <= 1e-12 * mean:
+            hi -= 1
+        else:
+            lo += 1
+    return send
+
+
+def test_plan_matches_the_reference_pairing_rules(built):
+    from dfchem_host import balance
+
+    rng = np.random.default_rng(3)
+    for n in (2, 3, 4, 8):
+        for _ in range(20):
+            loads = rng.uniform(1.0, 100.0, n)
+            for alg in (balance.ALL_AVERAGE, balance.HEAD_TAIL):
+                send = balance.plan_matrix(loads, alg)
+                assert np.allclose(send, _reference_pairing(loads, alg == balance.HEAD_TAIL), rtol=1e-12, atol=1e-9), (n, alg, loads)
+                assert (np.diag(send) == 0).all() and (send >= 0).all()
+                # a rank is sender or receiver, never both (runtime_assert in the reference)
+                assert not ((send.sum(1) > 0) & (send.sum(0) > 0)).any()
 
 
 def test_plan_moves_load_towards_the_mean(built):
@@ -27,9 +80,11 @@ def test_plan_moves_load_towards_the_mean(built):
 
     loads = np.array([100.0, 20.0, 60.0, 20.0])
     send = balance.plan_matrix(loads)
-    assert send.shape == (4, 4) and (np.diag(send) == 0).all() and (send >= 0).all()
     after = loads - send.sum(1) + send.sum(0)
     assert np.allclose(after, loads.mean())
+    ht = balance.plan_matrix(loads, balance.HEAD_TAIL)
+    after_ht = loads - ht.sum(1) + ht.sum(0)
+    assert after_ht.max() - after_ht.min() < loads.max() - loads.min() and np.isclose(after_ht.sum(), loads.sum())
     # operations below 1 % of the mean are dropped (LoadBalancer.C:170-178)
     assert (balance.plan_matrix(np.array([50.2, 49.8])) == 0).all()
 
@@ -64,10 +119,10 @@ def _worker(rank, world, port, tmp):
         ref = _stand_in_solve(fields)
         ok = bool(torch.equal(out, ref))
         moved = plan.n_send if rank == 0 else plan.n_recv
-        load_after = float(cost.sum()) - float(cost[plan.order[:plan.n_send]].sum())
+        load_after = float(cost.sum()) - float(cost[:plan.n_send].sum())
         got = torch.tensor([load_after], dtype=torch.float64)
         extra = [torch.zeros(1, dtype=torch.float64) for _ in range(world)]
-        sent_load = torch.tensor([float(cost[plan.order[:plan.n_send]].sum())], dtype=torch.float64)
+        sent_load = torch.tensor([float(cost[:plan.n_send].sum())], dtype=torch.float64)
         dist.all_gather(extra, sent_load)
         np.save(os.path.join(tmp, f"r{rank}.npy"),
                 np.array([float(ok), float(moved), float(got), float(plan.loads[0]), float(plan.loads[1]),

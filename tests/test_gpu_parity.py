@@ -135,12 +135,21 @@ def test_edge_cases(handles):
     sc, _ = h.solve(T, p, rho, 1e-6, np.ascontiguousarray(Ys))
     expect = full + (Y - Ys) / 1e-6 * rho[None]
     assert np.allclose(sc, expect, rtol=1e-9, atol=1e-9 * np.abs(expect).max())
-    # step budget exhausted -> per-cell status 1, finite output
+    # step budget exhausted -> DFCHEM_ECELLFAIL (the reference aborts on a CVODE failure), per-cell status 1, and
+    # every output array still written and finite
+    import dfchem_host
+
     h.lib.dfchem_set_max_steps(h.h, 2)
     st = np.zeros(T.shape[0], np.int32)
-    RRm, _ = h.solve(T, p, rho, 1e-6, Y, status=st)
-    h.lib.dfchem_set_max_steps(h.h, 20000)
+    RRm = np.full((N, T.shape[0]), np.nan)
+    with pytest.raises(dfchem_host.DfchemError) as ei:
+        h.solve(T, p, rho, 1e-6, Y, RR=RRm, status=st)
+    assert ei.value.code == dfchem_host.ECELLFAIL and b"integrator failed" in h.lib.dfchem_last_error(h.h)
     assert (st == 1).any() and set(st) <= {0, 1} and np.isfinite(RRm).all()
+    assert h.counters()["failed"] == int((st != 0).sum())
+    with pytest.raises(dfchem_host.DfchemError):          # ... also when the caller passes no status array
+        h.solve(T, p, rho, 1e-6, Y)
+    h.lib.dfchem_set_max_steps(h.h, 20000)
     # bad arguments
     assert h.lib.dfchem_solve(h.h, 4, T.ctypes.data, p.ctypes.data, rho.ctypes.data, None, 1e-6, Y.ctypes.data, 2,
                               full.ctypes.data, 4, qz.ctypes.data, None, None) == -1
