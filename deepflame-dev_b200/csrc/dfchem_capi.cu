@@ -77,6 +77,8 @@ struct dfchem_ctx {
     DevBuf d_transport;                       // transport fit tables (dfchem_set_transport_fits)
     TransportTab tt{};
     int thermo_ctas = 0;                      // resident thermo_kernel CTAs per SM (occupancy query, cached)
+    int thermo_pair_ctas = 0;                 // resident thermo_pair_kernel CTAs per SM
+    int thermo_tma_ok = 0;                    // 0 unknown, 1 bulk-async thermo kernel usable, -1 tables + tiles exceed shared memory
     HostLpc lpc;                              // lane-per-cell tables (small mechanisms)
     void* d_lpc = nullptr;
     LpcMech lm{};
@@ -586,15 +588,72 @@ int dfchem_correct_thermo_dev(dfchem_handle h, int n, const double* he, const do
     const int N = h->mech.N;
     const size_t tsm = thermo_smem_bytes(N);
     if (tsm > 48 * 1024) return fail(h, DFCHEM_EUNSUPPORTED, "thermo kernel: species tables exceed 48 KB of shared memory");
-    if (h->thermo_ctas == 0) {  // persistent CTAs: two waves of what is resident (the measured configuration)
-        int nb = 0;
-        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, thermo_kernel, 256, tsm));
-        h->thermo_ctas = std::max(1, nb);
+    // Kernel choice (DFCHEM_THERMO = pair | ldg | tma forces one; measured on B200, profiles/r2/thermo_variants.json):
+    //   pair  two cells per thread, 16-byte loads (default when every row is 16-byte aligned)
+    //   ldg   one cell per thread, 8-byte loads (round 1's kernel; ragged tails and misaligned callers)
+    //   tma   species rows staged by the bulk-copy engine (cp.async.bulk + mbarrier): correct but 1.5x slower here,
+    //         because one thread per cell and two 78 KB stages leave 8 warps per SM for the Newton arithmetic
+    static const std::string variant = [] { const char* e = std::getenv("DFCHEM_THERMO"); return std::string(e ? e : "pair"); }();
+    int done = 0;
+    auto aligned = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
+    const bool rows_aligned = (ldY % 2) == 0 && aligned(Y) && aligned(he) && aligned(p) && aligned(T) && aligned(psi) && aligned(rho) &&
+                              (!cp || aligned(cp)) && (!hai || (aligned(hai) && (ldH % 2) == 0));
+    if (variant == "tma" && n >= kTmaTile && rows_aligned) {
+        if (h->thermo_tma_ok == 0) {
+            int max_optin = 0;
+            CUDA_TRY(h, cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+            h->thermo_tma_ok = thermo_tma_smem_bytes(N) <= (size_t)max_optin ? 1 : -1;
+            if (h->thermo_tma_ok == 1)
+                CUDA_TRY(h, cudaFuncSetAttribute(thermo_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin));
+        }
+        if (h->thermo_tma_ok == 1) {
+            const int ntiles = n / kTmaTile;
+            thermo_tma_kernel<<<std::min(ntiles, h->sm_count), kTmaTile, thermo_tma_smem_bytes(N), s>>>(
+                h->dm, ntiles, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
+            CUDA_TRY(h, cudaGetLastError());
+            done = ntiles * kTmaTile;
+        }
+    } else if (variant == "pair" && n >= 2 && rows_aligned) {
+        const int npairs = n / 2;
+        // register budget / load batch of the pair kernel: (3 CTAs per SM, 6 loads) unless DFCHEM_THERMO_CFG=<minb><batch> says otherwise
+        static const int cfg = [] { const char* e = std::getenv("DFCHEM_THERMO_CFG"); return e ? std::atoi(e) : 36; }();
+        auto run = [&](auto kern) -> int {
+            if (h->thermo_pair_ctas == 0) {
+                int nb = 0;
+                CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, 256, tsm));
+                h->thermo_pair_ctas = std::max(1, nb);
+            }
+            static const int waves_env = [] { const char* e = std::getenv("DFCHEM_THERMO_WAVES"); return e ? std::max(1, std::atoi(e)) : 2; }();
+            const int grid = std::min((npairs + 255) / 256, h->sm_count * h->thermo_pair_ctas * waves_env);
+            kern<<<grid, 256, tsm, s>>>(h->dm, npairs, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
+            CUDA_TRY(h, cudaGetLastError());
+            return DFCHEM_OK;
+        };
+        int rc = DFCHEM_OK;
+        switch (cfg) {
+            case 26: rc = run(thermo_pair_kernel<2, 6>); break;
+            case 28: rc = run(thermo_pair_kernel<2, 8>); break;
+            case 34: rc = run(thermo_pair_kernel<3, 4>); break;
+            case 44: rc = run(thermo_pair_kernel<4, 4>); break;
+            case 43: rc = run(thermo_pair_kernel<4, 3>); break;
+            default: rc = run(thermo_pair_kernel<3, 6>); break;
+        }
+        if (rc != DFCHEM_OK) return rc;
+        done = 2 * npairs;
     }
-    static const int waves_env = [] { const char* e = std::getenv("DFCHEM_THERMO_WAVES"); return e ? std::max(1, std::atoi(e)) : 2; }();
-    const int grid = std::min((n + 255) / 256, h->sm_count * h->thermo_ctas * waves_env);
-    thermo_kernel<<<grid, 256, tsm, s>>>(h->dm, n, he, p, Y, ldY, T, psi, rho, cp, hai, ldH);
-    CUDA_TRY(h, cudaGetLastError());
+    if (done < n) {
+        const int nr = n - done;
+        if (h->thermo_ctas == 0) {  // persistent CTAs: two waves of what is resident (the measured configuration)
+            int nb = 0;
+            CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, thermo_kernel, 256, tsm));
+            h->thermo_ctas = std::max(1, nb);
+        }
+        static const int waves_env = [] { const char* e = std::getenv("DFCHEM_THERMO_WAVES"); return e ? std::max(1, std::atoi(e)) : 2; }();
+        const int grid = std::min((nr + 255) / 256, h->sm_count * h->thermo_ctas * waves_env);
+        thermo_kernel<<<grid, 256, tsm, s>>>(h->dm, nr, he + done, p + done, Y + done, ldY, T + done, psi + done, rho + done,
+                                             cp ? cp + done : nullptr, hai ? hai + done : nullptr, ldH);
+        CUDA_TRY(h, cudaGetLastError());
+    }
     return DFCHEM_OK;
 }
 

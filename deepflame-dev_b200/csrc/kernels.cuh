@@ -238,7 +238,7 @@ __device__ __forceinline__ ThermoSmem stage_thermo_tables(const DevMech& m, doub
     __syncthreads();
     return ThermoSmem{rec, Tsw, n_sw, slots, by_interval};
 }
-inline size_t thermo_smem_bytes(int N) { return ((size_t)N * (kThermoMaxSw + 1) * 8 + ((N + 3) & ~1)) * sizeof(double); }
+__host__ __device__ inline size_t thermo_smem_bytes(int N) { return ((size_t)N * (kThermoMaxSw + 1) * 8 + ((N + 3) & ~1)) * sizeof(double); }
 
 // record of species k for temperature Tq (hai / enthalpy loops: one species at a time)
 __device__ __forceinline__ const double* thermo_record(const ThermoSmem& t, int k, double Tq, int interval) {
@@ -360,6 +360,293 @@ thermo_kernel(const DevMech m, int n, const double* __restrict__ he, const doubl
                 hai[(size_t)k * ldH + c] = hrt * RT;  // the record holds a_j / W
             }
         }
+    }
+}
+
+// ---- thermo, two cells per thread: 16-byte loads, table records shared by both cells ---------------------------------
+// Same mixture-polynomial Newton as thermo_kernel, but a thread owns the cell PAIR (2c, 2c + 1): every species row
+// is read with one 16-byte load per thread (half the load instructions per byte) and every table record fetched from
+// shared memory feeds two cells, so the instruction count per cell drops by about a third -- the register-staged
+// kernel is co-limited by issue slots and HBM.  Requires even ldY and 16-byte aligned bases; the
+// caller runs thermo_kernel on an odd last cell.
+struct ThermoAcc {
+    double b0, b1, b2, b3, b4, b5, ys, rs;
+};
+__device__ __forceinline__ void thermo_acc(ThermoAcc& a, double y, const double2 a01, const double2 a23, const double2 a45, double rw) {
+    a.ys += y;
+    a.rs = fma(y, rw, a.rs);
+    a.b0 = fma(y, a01.x, a.b0);
+    a.b1 = fma(y, a01.y, a.b1);
+    a.b2 = fma(y, a23.x, a.b2);
+    a.b3 = fma(y, a23.y, a.b3);
+    a.b4 = fma(y, a45.x, a.b4);
+    a.b5 = fma(y, a45.y, a.b5);
+}
+// Newton on the mixture polynomial of one cell; returns T, sets cp and rw (= sum Y/W / sum Y)
+__device__ __forceinline__ double thermo_newton(const ThermoAcc& a, double htarget, double Tc, double& cp, double& rw) {
+    const double sc = kGasConstant / a.ys;
+    rw = a.rs / a.ys;
+    const double B0 = a.b0 * sc, B1 = a.b1 * sc, B2 = a.b2 * sc, B3 = a.b3 * sc, B4 = a.b4 * sc, B5 = a.b5 * sc;
+    const double H1 = B1 * 0.5, H2 = B2 * (1.0 / 3.0), H3 = B3 * 0.25, H4 = B4 * 0.2;
+    for (int it = 0; it < 60; ++it) {
+        const double h = B5 + Tc * (B0 + Tc * (H1 + Tc * (H2 + Tc * (H3 + Tc * H4))));
+        cp = B0 + Tc * (B1 + Tc * (B2 + Tc * (B3 + Tc * B4)));
+        double dT = (h - htarget) / cp;
+        dT = fmax(-100.0, fmin(100.0, dT));
+        Tc -= dT;
+        if (fabs(dT) < 1e-10 * Tc) break;
+    }
+    cp = B0 + Tc * (B1 + Tc * (B2 + Tc * (B3 + Tc * B4)));
+    return Tc;
+}
+__device__ __forceinline__ bool thermo_consistent(const ThermoSmem& t, double Tsel, double Tc) {
+    bool ok = true;
+    for (int j = 0; j < t.n_sw; ++j) {
+        const double tm = t.Tsw[j];
+        ok = ok && (((Tsel <= tm) == (Tc <= tm)) || fabs(Tc - tm) <= 1e-9 * tm);
+    }
+    return ok;
+}
+
+// MINB: resident CTAs per SM the register budget is set for; BATCH: 16-byte loads issued back to back
+template <int MINB, int BATCH>
+__global__ void __launch_bounds__(256, MINB)
+thermo_pair_kernel(const DevMech m, int npairs, const double* __restrict__ he, const double* __restrict__ p,
+                   const double* __restrict__ Y, int ldY, double* __restrict__ T, double* __restrict__ psi,
+                   double* __restrict__ rho, double* __restrict__ cp_out, double* __restrict__ hai, int ldH) {
+    extern __shared__ double2 dfc_smem[];
+    const ThermoSmem t = stage_thermo_tables(m, reinterpret_cast<double*>(dfc_smem));
+    const int N = m.N;
+    const int stride = t.slots * 8;
+    const size_t ld2 = (size_t)ldY / 2;   // row pitch in double2
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < npairs; c += gridDim.x * blockDim.x) {
+        const double2 ht = reinterpret_cast<const double2*>(he)[c];
+        const double2* __restrict__ Yc = reinterpret_cast<const double2*>(Y) + c;
+        const double2 Tg = reinterpret_cast<const double2*>(T)[c];
+        double Ta = Tg.x, Tb = Tg.y, Tsa = Ta, Tsb = Tb;   // estimates and the temperatures the ranges are selected at
+        double rwa = 0.0, rwb = 0.0, cpa = 0.0, cpb = 0.0;
+        bool donea = false, doneb = false;
+        for (int pass = 0; pass < 4 && !(donea && doneb); ++pass) {
+            ThermoAcc A{0, 0, 0, 0, 0, 0, 0, 0}, B{0, 0, 0, 0, 0, 0, 0, 0};
+            // both cells of a pair nearly always sit in the same table interval: then one record serves both
+            const int iva = t.by_interval ? thermo_interval(t, Tsa) : 0, ivb = t.by_interval ? thermo_interval(t, Tsb) : 0;
+            const bool shared_rec = t.by_interval && iva == ivb;
+            const double* ra = t.rec + iva * 8;
+            const double* rbp = t.rec + ivb * 8;
+            const double2* __restrict__ yp = Yc;
+            int k0 = 0;
+            for (; k0 + BATCH <= N; k0 += BATCH) {
+                double2 yv[BATCH];
+#pragma unroll
+                for (int u = 0; u < BATCH; ++u) {
+                    yv[u] = *yp;
+                    yp += ld2;
+                }
+#pragma unroll
+                for (int u = 0; u < BATCH; ++u) {
+                    const double* r = ra + (size_t)(k0 + u) * stride;
+                    if (shared_rec) {
+                        const double2* q = reinterpret_cast<const double2*>(r);
+                        const double2 a01 = q[0], a23 = q[1], a45 = q[2];
+                        const double w = r[6];
+                        thermo_acc(A, yv[u].x, a01, a23, a45, w);
+                        thermo_acc(B, yv[u].y, a01, a23, a45, w);
+                    } else {
+                        const double* r1 = r;
+                        const double* r2 = rbp + (size_t)(k0 + u) * stride;
+                        if (!t.by_interval) {
+                            r1 += (Tsa <= r1[7]) ? 0 : 8;
+                            r2 += (Tsb <= r2[7]) ? 0 : 8;
+                        }
+                        const double2* q1 = reinterpret_cast<const double2*>(r1);
+                        const double2* q2 = reinterpret_cast<const double2*>(r2);
+                        thermo_acc(A, yv[u].x, q1[0], q1[1], q1[2], r1[6]);
+                        thermo_acc(B, yv[u].y, q2[0], q2[1], q2[2], r2[6]);
+                    }
+                }
+            }
+            for (; k0 < N; ++k0, yp += ld2) {
+                const double2 y = *yp;
+                const double* r1 = ra + (size_t)k0 * stride;
+                const double* r2 = rbp + (size_t)k0 * stride;
+                if (!t.by_interval) {
+                    r1 += (Tsa <= r1[7]) ? 0 : 8;
+                    r2 += (Tsb <= r2[7]) ? 0 : 8;
+                }
+                const double2* q1 = reinterpret_cast<const double2*>(r1);
+                const double2* q2 = reinterpret_cast<const double2*>(r2);
+                thermo_acc(A, y.x, q1[0], q1[1], q1[2], r1[6]);
+                thermo_acc(B, y.y, q2[0], q2[1], q2[2], r2[6]);
+            }
+            if (!donea) {
+                Ta = thermo_newton(A, ht.x, Ta, cpa, rwa);
+                donea = thermo_consistent(t, Tsa, Ta);
+                if (!donea) Tsa = Ta;
+            }
+            if (!doneb) {
+                Tb = thermo_newton(B, ht.y, Tb, cpb, rwb);
+                doneb = thermo_consistent(t, Tsb, Tb);
+                if (!doneb) Tsb = Tb;
+            }
+        }
+        reinterpret_cast<double2*>(T)[c] = make_double2(Ta, Tb);
+        const double psa = 1.0 / (rwa * kGasConstant * Ta), psb = 1.0 / (rwb * kGasConstant * Tb);
+        reinterpret_cast<double2*>(psi)[c] = make_double2(psa, psb);
+        const double2 pp = reinterpret_cast<const double2*>(p)[c];
+        reinterpret_cast<double2*>(rho)[c] = make_double2(pp.x * psa, pp.y * psb);
+        if (cp_out) reinterpret_cast<double2*>(cp_out)[c] = make_double2(cpa, cpb);
+        if (hai) {
+            const double RTa = kGasConstant * Ta, rTa = 1.0 / Ta, RTb = kGasConstant * Tb, rTb = 1.0 / Tb;
+            const int iva = thermo_interval(t, Ta), ivb = thermo_interval(t, Tb);
+            double2* __restrict__ hp = reinterpret_cast<double2*>(hai) + c;
+            const size_t ldh2 = (size_t)ldH / 2;
+#pragma unroll 4
+            for (int k = 0; k < N; ++k) {
+                const double2* a = reinterpret_cast<const double2*>(thermo_record(t, k, Ta, iva));
+                const double2* b = reinterpret_cast<const double2*>(thermo_record(t, k, Tb, ivb));
+                const double2 a01 = a[0], a23 = a[1], a45 = a[2], b01 = b[0], b23 = b[1], b45 = b[2];
+                const double ha = a01.x + Ta * (a01.y * 0.5 + Ta * (a23.x * (1.0 / 3.0) + Ta * (a23.y * 0.25 + Ta * (a45.x * 0.2)))) + a45.y * rTa;
+                const double hb = b01.x + Tb * (b01.y * 0.5 + Tb * (b23.x * (1.0 / 3.0) + Tb * (b23.y * 0.25 + Tb * (b45.x * 0.2)))) + b45.y * rTb;
+                hp[(size_t)k * ldh2] = make_double2(ha * RTa, hb * RTb);
+            }
+        }
+    }
+}
+
+// ---- thermo, bulk-async form: species rows staged by the copy engine (cp.async.bulk + mbarrier) --------------------
+// The species-major layout is a perfect 2-D tile: (N + 3) rows x kTmaTile consecutive cells.  One elected thread asks
+// the bulk-copy engine for the (N + 3) row slices of the NEXT tile (2 KB each, 78 KB per gri30 tile) while the CTA's
+// threads run the mixture-polynomial Newton on the CURRENT tile out of shared memory: the bytes in flight per SM no
+// longer depend on registers or resident warps.  Two stages; a CTA-wide barrier hands a consumed stage back.
+// Requirements: 16-byte aligned rows (even ldY, aligned bases); full tiles only (the caller runs thermo_kernel on
+// the ragged tail).
+constexpr int kTmaTile = 256;
+constexpr int kTmaStages = 2;
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+inline size_t thermo_tma_smem_bytes(int N) {
+    return thermo_smem_bytes(N) + (size_t)kTmaStages * (N + 3) * kTmaTile * sizeof(double) + 64;
+}
+
+__global__ void __launch_bounds__(kTmaTile, 1)
+thermo_tma_kernel(const DevMech m, int ntiles, const double* __restrict__ he, const double* __restrict__ p,
+                  const double* __restrict__ Y, int ldY, double* __restrict__ T, double* __restrict__ psi,
+                  double* __restrict__ rho, double* __restrict__ cp_out, double* __restrict__ hai, int ldH) {
+    extern __shared__ double2 dfc_smem[];
+    double* smem = reinterpret_cast<double*>(dfc_smem);
+    const ThermoSmem t = stage_thermo_tables(m, smem);
+    const int N = m.N, rows = N + 3;
+    double* tiles = smem + (thermo_smem_bytes(N) / sizeof(double));                 // [stages][rows][kTmaTile]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + (size_t)kTmaStages * rows * kTmaTile);
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        for (int s = 0; s < kTmaStages; ++s) mbar_init(bars + s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto prefetch = [&](int tile, int stage) {   // one thread: arm the barrier, then one bulk copy per row slice
+        double* dst = tiles + (size_t)stage * rows * kTmaTile;
+        const size_t c0 = (size_t)tile * kTmaTile;
+        constexpr uint32_t rb = kTmaTile * sizeof(double);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy reads of this stage are done
+        mbar_expect_tx(bars + stage, (uint32_t)rows * rb);
+        for (int k = 0; k < N; ++k) bulk_g2s(dst + (size_t)k * kTmaTile, Y + (size_t)k * ldY + c0, rb, bars + stage);
+        bulk_g2s(dst + (size_t)N * kTmaTile, he + c0, rb, bars + stage);
+        bulk_g2s(dst + (size_t)(N + 1) * kTmaTile, p + c0, rb, bars + stage);
+        bulk_g2s(dst + (size_t)(N + 2) * kTmaTile, T + c0, rb, bars + stage);
+    };
+    if (tid == 0 && (int)blockIdx.x < ntiles) prefetch(blockIdx.x, 0);
+    const int stride = t.slots * 8;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const int stage = it % kTmaStages;
+        if (tid == 0 && tile + (int)gridDim.x < ntiles) prefetch(tile + gridDim.x, (it + 1) % kTmaStages);
+        mbar_wait(bars + stage, (uint32_t)(it / kTmaStages) & 1u);
+        const double* ys = tiles + (size_t)stage * rows * kTmaTile + tid;
+        const size_t c = (size_t)tile * kTmaTile + tid;
+        const double htarget = ys[(size_t)N * kTmaTile];
+        const double pc = ys[(size_t)(N + 1) * kTmaTile];
+        double Tc = ys[(size_t)(N + 2) * kTmaTile];
+        double Tsel = Tc, rw = 0.0, cp = 0.0;
+        for (int pass = 0; pass < 4; ++pass) {
+            const double* rb = t.rec + (t.by_interval ? thermo_interval(t, Tsel) * 8 : 0);
+            double b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0, b4 = 0.0, b5 = 0.0, ysum = 0.0, rs = 0.0;
+#pragma unroll 4
+            for (int k = 0; k < N; ++k) {
+                const double y = ys[(size_t)k * kTmaTile];
+                const double* r = rb + (size_t)k * stride;
+                if (!t.by_interval) r += (Tsel <= r[7]) ? 0 : 8;
+                const double2* a = reinterpret_cast<const double2*>(r);
+                const double2 a01 = a[0], a23 = a[1], a45 = a[2];
+                ysum += y;
+                rs = fma(y, r[6], rs);
+                b0 = fma(y, a01.x, b0);
+                b1 = fma(y, a01.y, b1);
+                b2 = fma(y, a23.x, b2);
+                b3 = fma(y, a23.y, b3);
+                b4 = fma(y, a45.x, b4);
+                b5 = fma(y, a45.y, b5);
+            }
+            const double sc = kGasConstant / ysum;
+            rw = rs / ysum;
+            const double B0 = b0 * sc, B1 = b1 * sc, B2 = b2 * sc, B3 = b3 * sc, B4 = b4 * sc, B5 = b5 * sc;
+            const double H1 = B1 * 0.5, H2 = B2 * (1.0 / 3.0), H3 = B3 * 0.25, H4 = B4 * 0.2;
+            for (int itn = 0; itn < 60; ++itn) {
+                const double h = B5 + Tc * (B0 + Tc * (H1 + Tc * (H2 + Tc * (H3 + Tc * H4))));
+                cp = B0 + Tc * (B1 + Tc * (B2 + Tc * (B3 + Tc * B4)));
+                double dT = (h - htarget) / cp;
+                dT = fmax(-100.0, fmin(100.0, dT));
+                Tc -= dT;
+                if (fabs(dT) < 1e-10 * Tc) break;
+            }
+            cp = B0 + Tc * (B1 + Tc * (B2 + Tc * (B3 + Tc * B4)));
+            bool consistent = true;
+            for (int j = 0; j < t.n_sw; ++j) {
+                const double tm = t.Tsw[j];
+                consistent = consistent && (((Tsel <= tm) == (Tc <= tm)) || fabs(Tc - tm) <= 1e-9 * tm);
+            }
+            if (consistent) break;
+            Tsel = Tc;
+        }
+        T[c] = Tc;
+        const double ps = 1.0 / (rw * kGasConstant * Tc);
+        psi[c] = ps;
+        rho[c] = pc * ps;
+        if (cp_out) cp_out[c] = cp;
+        if (hai) {
+            const double RT = kGasConstant * Tc, rT = 1.0 / Tc;
+            const int iv = thermo_interval(t, Tc);
+#pragma unroll 4
+            for (int k = 0; k < N; ++k) {
+                const double2* a = reinterpret_cast<const double2*>(thermo_record(t, k, Tc, iv));
+                const double2 a01 = a[0], a23 = a[1], a45 = a[2];
+                const double hrt = a01.x + Tc * (a01.y * 0.5 + Tc * (a23.x * (1.0 / 3.0) + Tc * (a23.y * 0.25 + Tc * (a45.x * 0.2)))) +
+                                   a45.y * rT;
+                hai[(size_t)k * ldH + c] = hrt * RT;
+            }
+        }
+        __syncthreads();   // every thread has finished reading this stage: the next prefetch may overwrite it
     }
 }
 

@@ -103,5 +103,5 @@ def test_two_rank_nccl_rebalance_is_bit_identical(built, tmp_path, alg):
     assert r0[0] == 1.0 and r1[0] == 1.0                  # RR, Qdot, cost, status bit-identical to the unbalanced call
     assert r0[1] > 0 and r0[2] == 0                       # the hot rank sent cells and received none
     assert r1[2] == r0[1] and r1[1] == 0                  # ... and the cold rank received exactly those
-    assert r0[4] > 2.0 * r1[4]                            # the loads were unequal to begin with
+    assert r0[4] > 1.5 * r1[4]                            # the loads were unequal to begin with
     print("two-rank rebalance: cells moved", int(r0[1]), "bytes", int(r0[3] + r1[3]), "loads", r0[4], r1[4], "ms", r0[5], r1[5])
