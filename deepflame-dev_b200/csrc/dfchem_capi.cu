@@ -588,12 +588,14 @@ int dfchem_correct_thermo_dev(dfchem_handle h, int n, const double* he, const do
     const int N = h->mech.N;
     const size_t tsm = thermo_smem_bytes(N);
     if (tsm > 48 * 1024) return fail(h, DFCHEM_EUNSUPPORTED, "thermo kernel: species tables exceed 48 KB of shared memory");
-    // Kernel choice (DFCHEM_THERMO = pair | ldg | tma forces one; measured on B200, profiles/r2/thermo_variants.json):
-    //   pair  two cells per thread, 16-byte loads (default when every row is 16-byte aligned)
-    //   ldg   one cell per thread, 8-byte loads (round 1's kernel; ragged tails and misaligned callers)
-    //   tma   species rows staged by the bulk-copy engine (cp.async.bulk + mbarrier): correct but 1.5x slower here,
-    //         because one thread per cell and two 78 KB stages leave 8 warps per SM for the Newton arithmetic
-    static const std::string variant = [] { const char* e = std::getenv("DFCHEM_THERMO"); return std::string(e ? e : "pair"); }();
+    // Kernel choice (DFCHEM_THERMO = ldg | pair | tma; measured on B200, profiles/r2/thermo_variants.json, gri30 4M cells):
+    //   ldg   one cell per thread, 8-byte loads, 32 warps/SM                          0.40 ms  (default)
+    //   pair  two cells per thread, 16-byte loads, a third fewer instructions per cell 0.57 ms  (16 warps/SM at 128 registers)
+    //   tma   species rows staged by the bulk-copy engine (cp.async.bulk + mbarrier)    0.60 ms  (8 warps/SM: one thread per
+    //         cell and two 78 KB stages)
+    // The kernel is latency-bound per warp; resident warps with loads in flight beat both fewer instructions and
+    // copy-engine staging.  The two experiments stay selectable so that the comparison can be re-run.
+    static const std::string variant = [] { const char* e = std::getenv("DFCHEM_THERMO"); return std::string(e ? e : "ldg"); }();
     int done = 0;
     auto aligned = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
     const bool rows_aligned = (ldY % 2) == 0 && aligned(Y) && aligned(he) && aligned(p) && aligned(T) && aligned(psi) && aligned(rho) &&
@@ -936,6 +938,64 @@ int dfchem_transport(dfchem_handle h, int n, const double* T, const double* p, c
     if (rhoD)
         CUDA_TRY(h, cudaMemcpy2DAsync(rhoD, (size_t)ldD * sizeof(double), dD, nb, nb, N, cudaMemcpyDeviceToHost, s));
     CUDA_TRY(h, cudaStreamSynchronize(s));
+    return DFCHEM_OK;
+}
+
+// ---- boundary faces of correctThermo (dfChemistryModel.C:546-727; device precedent src_gpu/dfThermo.cu:603-657) -------
+int dfchem_correct_thermo_patches_dev(dfchem_handle h, int n_patches, const int* patch_size, const int* patch_type,
+                                      int n_boundary, double* b_he, const double* b_p, const double* b_Y, double* b_T,
+                                      double* b_psi, double* b_rho, double* b_cp, double* b_mu, double* b_alpha,
+                                      double* b_rhoD, int unity_lewis, int n_cells, const int* face_cell,
+                                      const double* T, const double* he, const double* psi, const double* rho,
+                                      const double* mu, const double* alpha, const double* rhoD, void* stream) {
+    if (!h) return DFCHEM_EINVAL;
+    if (n_patches < 0 || (n_patches > 0 && (!patch_size || !patch_type)) || n_boundary < 0 || !b_he || !b_p || !b_Y || !b_T ||
+        !b_psi || !b_rho || !b_cp)
+        return fail(h, DFCHEM_EINVAL, "dfchem_correct_thermo_patches_dev: bad argument");
+    const bool transport = b_mu || b_alpha || b_rhoD;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int offset = 0;
+    for (int i = 0; i < n_patches; ++i) {
+        const int sz = patch_size[i], ty = patch_type[i];
+        if (sz < 0 || ty < 0 || ty > 2) return fail(h, DFCHEM_EINVAL, "dfchem_correct_thermo_patches_dev: bad patch table");
+        const int span = ty == DFCHEM_PATCH_PROCESSOR ? 2 * sz : sz;
+        if (offset + span > n_boundary) return fail(h, DFCHEM_EINVAL, "dfchem_correct_thermo_patches_dev: patches exceed n_boundary");
+        if (sz > 0) {
+            int rc;
+            if (ty == DFCHEM_PATCH_FIXED_T) {   // T is given: he <- h(T, Y) first (dfChemistryModel.C:572-589); the Newton solve then returns T
+                rc = dfchem_h_from_T_dev(h, sz, b_T + offset, b_Y + offset, n_boundary, b_he + offset, stream);
+                if (rc != DFCHEM_OK) return rc;
+            }
+            rc = dfchem_correct_thermo_dev(h, sz, b_he + offset, b_p + offset, b_Y + offset, n_boundary, b_T + offset, b_psi + offset,
+                                           b_rho + offset, b_cp + offset, nullptr, n_boundary, stream);
+            if (rc != DFCHEM_OK) return rc;
+            if (transport) {
+                rc = dfchem_transport_dev(h, sz, b_T + offset, b_p + offset, b_rho + offset, b_cp + offset, b_Y + offset, n_boundary,
+                                          b_mu ? b_mu + offset : nullptr, b_alpha ? b_alpha + offset : nullptr,
+                                          b_rhoD ? b_rhoD + offset : nullptr, n_boundary, unity_lewis, stream);
+                if (rc != DFCHEM_OK) return rc;
+            }
+            if (ty == DFCHEM_PATCH_PROCESSOR) {   // internal side of a processor patch = the owner cells' values
+                if (!face_cell || !T || !he || !psi || !rho || n_cells <= 0)
+                    return fail(h, DFCHEM_EINVAL, "dfchem_correct_thermo_patches_dev: processor patch needs the internal fields and face_cell");
+                PatchRows rows{};
+                int nr = 0;
+                auto add = [&](const double* in, double* bnd) {
+                    if (in && bnd) {
+                        rows.in[nr] = in;
+                        rows.bnd[nr] = bnd;
+                        ++nr;
+                    }
+                };
+                add(T, b_T); add(he, b_he); add(psi, b_psi); add(rho, b_rho); add(mu, b_mu); add(alpha, b_alpha);
+                const bool sp = rhoD && b_rhoD;
+                patch_internal_side_kernel<<<std::max(1, std::min((sz + 255) / 256, h->sm_count * 4)), 256, 0, s>>>(
+                    rows, nr, sz, offset, face_cell, rhoD, b_rhoD, sp ? h->mech.N : 0, (size_t)n_cells, (size_t)n_boundary);
+                CUDA_TRY(h, cudaGetLastError());
+            }
+        }
+        offset += span;
+    }
     return DFCHEM_OK;
 }
 

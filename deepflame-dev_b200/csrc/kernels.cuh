@@ -650,6 +650,24 @@ thermo_tma_kernel(const DevMech m, int ntiles, const double* __restrict__ he, co
     }
 }
 
+// Processor patches carry 2 x size entries: [neighbour side | internal side]; the internal side is the owner
+// cell's value (correct_internal_boundary_field_scalar, src_gpu/dfMatrixOpBase.cu:387-399).  One launch copies
+// all `nrows` fields of a patch: rows[r] = (internal field, boundary field) pointers.
+struct PatchRows {
+    const double* in[8];
+    double* bnd[8];
+};
+__global__ void __launch_bounds__(256)
+patch_internal_side_kernel(PatchRows rows, int nrows, int size, int offset, const int* __restrict__ face_cell,
+                           const double* __restrict__ in_sp, double* __restrict__ bnd_sp, int n_sp, size_t ld_in, size_t ld_bnd) {
+    for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < size; f += gridDim.x * blockDim.x) {
+        const int cell = face_cell[offset + f];
+        const size_t dst = (size_t)offset + size + f;
+        for (int r = 0; r < nrows; ++r) rows.bnd[r][dst] = rows.in[r][cell];
+        for (int k = 0; k < n_sp; ++k) bnd_sp[(size_t)k * ld_bnd + dst] = in_sp[(size_t)k * ld_in + cell];   // rhoD_k
+    }
+}
+
 // FP64 roofline denominator: 16 independent DFMA chains per thread (MEASURED_PEAKS.json has no
 // FP64 entry).  2 flops per DFMA.
 __global__ void __launch_bounds__(256) fp64_peak_kernel(double* out, int iters, double seed) {

@@ -64,6 +64,7 @@ SIGNATURES = {
                                  c_void_p, c_void_p, c_void_p, c_int, c_int]),
     "dfchem_transport_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                                      c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "dfchem_correct_thermo_patches_dev": (c_int, [c_void_p, c_int, _ip, _ip, c_int] + [c_void_p] * 10 + [c_int, c_int] + [c_void_p] * 9),
     "dfchem_last_counters": (c_int, [c_void_p, POINTER(c_ulonglong)]),
     "dfchem_balance_plan": (c_int, [_dp, c_int, _dp]),
     "dfchem_balance_plan2": (c_int, [_dp, c_int, c_int, _dp]),

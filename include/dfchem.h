@@ -22,6 +22,8 @@
  *   dfchem_h_from_T[_dev]    dfChemistryModel::updateEnergy, dfChemistryModel.H:326-352, and the
  *                            fixesValue(T) patches of correctThermo :572-589; device precedent
  *                            dfThermo::updateEnergy src_gpu/dfThermo.cu:557-570
+ *   dfchem_correct_thermo_patches_dev   boundary loop of correctThermo, dfChemistryModel.C:546-727; device precedent
+ *                            src_gpu/dfThermo.cu:603-657 (per-patch launches, processor patches with 2x entries)
  *   dfchem_transport[_dev]   transport part of correctThermo, dfChemistryModel.C:513-541 (mu, alpha,
  *                            rhoD; UnityLewis :521-527); device precedent calculateViscosityGPU /
  *                            calculateThermoConductivityGPU / calculateRhoDGPU,
@@ -193,6 +195,22 @@ int dfchem_transport(dfchem_handle h, int n, const double* T, const double* p, c
 int dfchem_transport_dev(dfchem_handle h, int n, const double* T, const double* p,
                          const double* rho, const double* cp, const double* Y, int ldY, double* mu,
                          double* alpha, double* rhoD, int ldD, int unity_lewis, void* stream);
+
+/* Boundary faces of correctThermo (dfChemistryModel.C:546-727), device arrays laid out like the reference's
+ * dfMatrixDataBase boundary fields (src_gpu/dfThermo.cu:603-657): all patches back to back in arrays of n_boundary
+ * entries (species-major with leading dimension n_boundary), patch i occupying patch_size[i] entries -- twice that for
+ * a processor patch: [neighbour side | internal side].  Per patch: DFCHEM_PATCH_FIXED_T: T is given, he <- h(T, Y)
+ * (:572-589); otherwise T <- solve h(T, Y) = he; then psi, rho, cp and, when the output pointers are given, mu, alpha,
+ * rhoD; a processor patch then copies T, he, psi, rho, mu, alpha, rhoD of the owner cells (face_cell) into its internal
+ * side (correct_internal_boundary_field_scalar, src_gpu/dfMatrixOpBase.cu:387-399).  patch_size / patch_type are host
+ * arrays, everything else device memory; stream-ordered, no host synchronisation. */
+enum { DFCHEM_PATCH_GENERIC = 0, DFCHEM_PATCH_FIXED_T = 1, DFCHEM_PATCH_PROCESSOR = 2 };
+int dfchem_correct_thermo_patches_dev(dfchem_handle h, int n_patches, const int* patch_size, const int* patch_type,
+                                      int n_boundary, double* b_he, const double* b_p, const double* b_Y, double* b_T,
+                                      double* b_psi, double* b_rho, double* b_cp, double* b_mu, double* b_alpha,
+                                      double* b_rhoD, int unity_lewis, int n_cells, const int* face_cell,
+                                      const double* T, const double* he, const double* psi, const double* rho,
+                                      const double* mu, const double* alpha, const double* rhoD, void* stream);
 
 /* Counters of the last dfchem_solve* call, summed over its cells: [0] accepted steps, [1] rejected steps,
  * [2] cells with status != 0, [3] kernel launches issued by the last call.  After dfchem_solve_dev the
