@@ -556,10 +556,9 @@ def load_transport(h, mech, synth):
     """Transport fits for the bench's mu/alpha/rhoD leg: the mechanism compiler's own generator when the library
     has one (dfchem_generate_transport_fits), else synthetic fits of Cantera's functional form."""
     lib = h.lib
-    if hasattr(lib, "dfchem_generate_transport_fits"):
-        rc = lib.dfchem_generate_transport_fits(h.h)
-        if rc == 0:
-            return "generated by the mechanism compiler from the species' Lennard-Jones data (dfchem_generate_transport_fits)"
+    rc = lib.dfchem_generate_transport_fits(h.h, None, None, None)
+    if rc == 0:
+        return "generated by the mechanism compiler from the species' Lennard-Jones data (dfchem_generate_transport_fits)"
     visc, cond, diff = synth.synthetic_transport_fits(h.W)
     h.set_transport_fits(visc, cond, diff)
     return "synthetic (Cantera's ln T polynomial form)"

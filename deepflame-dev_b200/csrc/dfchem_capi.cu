@@ -14,6 +14,7 @@
 #include "kernels.cuh"
 #include "rebalance.cuh"
 #include "transport.cuh"
+#include "transport_fit.hpp"
 
 using namespace dfchem;
 
@@ -861,6 +862,19 @@ int dfchem_set_transport_fits(dfchem_handle h, const double* visc, const double*
         return fail(h, DFCHEM_EUNSUPPORTED, "transport kernel: species columns exceed the shared memory of one CTA");
     CUDA_TRY(h, cudaFuncSetAttribute(transport_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin));
     return DFCHEM_OK;
+}
+
+// Fits generated by the mechanism compiler from the species' Lennard-Jones data (transport_fit.cpp); optionally also
+// returned to the caller (visc[N*5], cond[N*5], diff[N*N*5], any may be NULL).
+int dfchem_generate_transport_fits(dfchem_handle h, double* visc_out, double* cond_out, double* diff_out) {
+    if (!h) return DFCHEM_EINVAL;
+    std::vector<double> visc, cond, diff;
+    if (!generate_transport_fits(h->mech, visc, cond, diff))
+        return fail(h, DFCHEM_EMECH, "dfchem_generate_transport_fits: the mechanism has no complete `transport:` data");
+    if (visc_out) std::copy(visc.begin(), visc.end(), visc_out);
+    if (cond_out) std::copy(cond.begin(), cond.end(), cond_out);
+    if (diff_out) std::copy(diff.begin(), diff.end(), diff_out);
+    return dfchem_set_transport_fits(h, visc.data(), cond.data(), diff.data());
 }
 
 // thermo_<mech>.txt of the reference (src_gpu/dfThermo.cu:361-435): int N; double W[N];

@@ -250,6 +250,25 @@ Mechanism compile(const yaml::Node& doc) {
         const double* a = T0 <= m.Tmid[k] ? &m.nasa_lo[(size_t)k * 7] : &m.nasa_hi[(size_t)k * 7];
         m.hc[k] = (nasa_h_RT(a, T0) * kGasConstant * T0) / m.W[k];
     }
+    // transport data (input of the fit generator, transport_fit.cpp); all species or none
+    m.trans.assign((size_t)N * 6, 0.0);
+    for (int k = 0; k < N && !m.trans.empty(); ++k) {
+        const yaml::Node& s = *by_name.find(m.species[k])->second;
+        if (!s.has("transport") || !s.at("transport").has("geometry") || !s.at("transport").has("well-depth") ||
+            !s.at("transport").has("diameter")) {
+            m.trans.clear();
+            break;
+        }
+        const yaml::Node& t = s.at("transport");
+        const std::string g = t.at("geometry").as_string();
+        double* r = &m.trans[(size_t)k * 6];
+        r[0] = g == "atom" ? 0.0 : (g == "linear" ? 1.0 : 2.0);
+        r[1] = t.at("well-depth").as_double();
+        r[2] = t.at("diameter").as_double();
+        r[3] = t.has("dipole") ? t.at("dipole").as_double() : 0.0;
+        r[4] = t.has("polarizability") ? t.at("polarizability").as_double() : 0.0;
+        r[5] = t.has("rotational-relaxation") ? t.at("rotational-relaxation").as_double() : 0.0;
+    }
 
     const yaml::Node& rx = doc.at("reactions");
     const int R = m.R = (int)rx.size();
@@ -386,6 +405,11 @@ std::vector<uint8_t> Mechanism::serialize() const {
     put(out, kind); put(out, reversible); put(out, r_idx); put(out, p_idx);
     put(out, A); put(out, b); put(out, Ta); put(out, A0); put(out, b0); put(out, Ta0);
     put(out, troe); put(out, r_nu); put(out, r_ord); put(out, p_nu); put(out, eff);
+    if (!trans.empty()) {
+        const char sec[8] = {'T', 'R', 'N', '1', 0, 0, 0, 0};
+        out.insert(out.end(), sec, sec + 8);
+        put(out, trans);
+    }
     return out;
 }
 
@@ -408,6 +432,10 @@ Mechanism Mechanism::deserialize(const uint8_t* data, size_t len) {
     get(p, end, m.A, R); get(p, end, m.b, R); get(p, end, m.Ta, R); get(p, end, m.A0, R); get(p, end, m.b0, R); get(p, end, m.Ta0, R);
     get(p, end, m.troe, R * 4); get(p, end, m.r_nu, R * kMaxSide); get(p, end, m.r_ord, R * kMaxSide); get(p, end, m.p_nu, R * kMaxSide);
     get(p, end, m.eff, R * N);
+    if ((size_t)(end - p) >= 8 && std::memcmp(p, "TRN1", 4) == 0) {
+        p += 8;
+        get(p, end, m.trans, N * 6);
+    }
     if (p != end) throw std::runtime_error("mechanism blob: trailing bytes");
     m.equations.assign(R, "");
     return m;

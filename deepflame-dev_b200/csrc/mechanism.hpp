@@ -42,8 +42,13 @@ struct Mechanism {
     std::vector<double> p_nu;           // [R*kMaxSide]
     std::vector<double> eff;            // [R*N] third-body efficiencies (1 for M-less reactions)
     std::vector<std::string> equations; // [R] diagnostic only (not serialised)
+    // Lennard-Jones / Stockmayer transport data of the species' `transport:` blocks (model: gas), [N*6]:
+    // geometry (0 atom, 1 linear, 2 nonlinear), well-depth [K], diameter [Angstrom], dipole [Debye],
+    // polarizability [Angstrom^3], rotational-relaxation.  Empty when any species lacks the block.
+    std::vector<double> trans;
 
-    // Flat little-endian blob "DFCHEMB1"; byte-identical to oracle/mech.py::serialize().
+    // Flat little-endian blob "DFCHEMB1" (+ optional trailing section "TRN1" with `trans`); byte-identical to
+    // oracle/mech.py::serialize().
     std::vector<uint8_t> serialize() const;
     static Mechanism deserialize(const uint8_t* data, size_t len);
 };

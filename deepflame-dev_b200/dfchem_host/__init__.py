@@ -60,6 +60,7 @@ SIGNATURES = {
     "dfchem_reaction_stoich": (c_int, [c_void_p, c_int, _dp]),
     "dfchem_set_transport_fits": (c_int, [c_void_p, _dp, _dp, _dp]),
     "dfchem_load_transport_file": (c_int, [c_void_p, c_char_p]),
+    "dfchem_generate_transport_fits": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "dfchem_transport": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                                  c_void_p, c_void_p, c_void_p, c_int, c_int]),
     "dfchem_transport_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
@@ -249,6 +250,12 @@ class Handle:
         diff = np.ascontiguousarray(diff, dtype=np.float64).reshape(self.N, self.N, 5)
         self.check(self.lib.dfchem_set_transport_fits(self.h, visc.ctypes.data_as(_dp), cond.ctypes.data_as(_dp),
                                                       diff.ctypes.data_as(_dp)))
+
+    def generate_transport_fits(self):
+        """Fits from the mechanism's own transport data (dfchem_generate_transport_fits); returns (visc, cond, diff)."""
+        visc, cond, diff = np.zeros((self.N, 5)), np.zeros((self.N, 5)), np.zeros((self.N, self.N, 5))
+        self.check(self.lib.dfchem_generate_transport_fits(self.h, _ptr(visc), _ptr(cond), _ptr(diff)))
+        return visc, cond, diff
 
     def load_transport_file(self, path):
         self.check(self.lib.dfchem_load_transport_file(self.h, os.fsencode(path)))

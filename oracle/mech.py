@@ -66,6 +66,7 @@ class Mechanism:
     p_nu: np.ndarray
     eff: np.ndarray           # [R,N] third-body efficiencies (rows of 1 for M-less reactions)
     equations: list[str] = field(default_factory=list)
+    trans: np.ndarray | None = None   # [N,6] geometry(0 atom,1 linear,2 nonlinear), well-depth K, diameter A, dipole D, polarizability A^3, Zrot
 
     @property
     def N(self):
@@ -185,6 +186,14 @@ def load_mechanism(path) -> Mechanism:
         else:
             Tlo[k], Tmid[k], Thi[k] = tr
             lo[k] = data[0]; hi[k] = data[1]
+    trans = np.zeros((N, 6))
+    for k, n in enumerate(names):
+        t = sp_defs[n].get("transport")
+        if not t or "geometry" not in t or "well-depth" not in t or "diameter" not in t:
+            trans = None
+            break
+        trans[k] = [{"atom": 0.0, "linear": 1.0}.get(str(t["geometry"]), 2.0), float(t["well-depth"]), float(t["diameter"]),
+                    float(t.get("dipole", 0.0)), float(t.get("polarizability", 0.0)), float(t.get("rotational-relaxation", 0.0))]
     T0 = 298.15
     hc = np.array([
         (nasa_h_RT(lo[k] if T0 <= Tmid[k] else hi[k], T0) * GAS_CONSTANT * T0) / W[k] for k in range(N)
@@ -244,7 +253,7 @@ def load_mechanism(path) -> Mechanism:
                 if str(n) in names:
                     eff[i, names.index(str(n))] = float(v)
     return Mechanism(names, elements, comp, W, Tlo, Tmid, Thi, lo, hi, hc, kind, rev, A, b, Ta,
-                     A0, b0, Ta0, troe, r_idx, r_nu, r_ord, p_idx, p_nu, eff, eqs)
+                     A0, b0, Ta0, troe, r_idx, r_nu, r_ord, p_idx, p_nu, eff, eqs, trans)
 
 
 # --------------------------------------------------------------------------------------
@@ -270,6 +279,9 @@ def serialize(m: Mechanism) -> bytes:
         i(a)
     for a in (m.A, m.b, m.Ta, m.A0, m.b0, m.Ta0, m.troe, m.r_nu, m.r_ord, m.p_nu, m.eff):
         d(a)
+    if m.trans is not None:          # optional trailing section: Lennard-Jones / Stockmayer data for the fit generator
+        out.append(b"TRN1\0\0\0\0")
+        d(m.trans)
     return b"".join(out)
 
 
@@ -299,6 +311,10 @@ def deserialize(buf: bytes) -> Mechanism:
     kind = i(R); rev = i(R); r_idx = i(R, ms); p_idx = i(R, ms)
     A = d(R); b = d(R); Ta = d(R); A0 = d(R); b0 = d(R); Ta0 = d(R)
     troe = d(R, 4); r_nu = d(R, ms); r_ord = d(R, ms); p_nu = d(R, ms); eff = d(R, N)
+    trans = None
+    if len(buf) - off >= 8 and buf[off:off + 4] == b"TRN1":
+        off += 8
+        trans = d(N, 6)
     assert off == len(buf)
     return Mechanism(names, elems, comp, W, Tlo, Tmid, Thi, lo, hi, hc, kind, rev, A, b, Ta,
-                     A0, b0, Ta0, troe, r_idx, r_nu, r_ord, p_idx, p_nu, eff, [])
+                     A0, b0, Ta0, troe, r_idx, r_nu, r_ord, p_idx, p_nu, eff, [], trans)

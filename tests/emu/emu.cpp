@@ -14,6 +14,7 @@
 #include "../../deepflame-dev_b200/csrc/cell_driver.cuh"
 #include "../../deepflame-dev_b200/csrc/lane_cell.cuh"
 #include "../../deepflame-dev_b200/csrc/dispatch.hpp"
+#include "../../deepflame-dev_b200/csrc/transport_fit.hpp"
 
 using namespace dfchem;
 
@@ -183,6 +184,16 @@ int emu_solve_lpc(void* h, int nC, const double* T, const double* p, const doubl
         counters[1] += S.rej;
         counters[2] += S.status != 0;
     }
+    return 0;
+}
+// the mechanism compiler's transport-fit generator (host code, no emulation involved); 0 ok, -2 no transport data
+int emu_transport_fits(void* h, double* visc, double* cond, double* diff) {
+    const Emu* e = static_cast<Emu*>(h);
+    std::vector<double> v, c, d;
+    if (!generate_transport_fits(e->mech, v, c, d)) return -2;
+    std::copy(v.begin(), v.end(), visc);
+    std::copy(c.begin(), c.end(), cond);
+    std::copy(d.begin(), d.end(), diff);
     return 0;
 }
 int emu_wdot(void* h, int nC, const double* T, const double* p, const double* Y, int ldY, double* wr,
