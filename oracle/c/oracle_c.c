@@ -55,6 +55,8 @@ Mech* oc_load(const void* blob, size_t len) {
     TAKE_D(A, R); TAKE_D(b, R); TAKE_D(Ta, R); TAKE_D(A0, R); TAKE_D(b0, R); TAKE_D(Ta0, R);
     TAKE_D(troe, 4 * R); TAKE_D(rnu, MAXS * R); TAKE_D(rord, MAXS * R); TAKE_D(pnu, MAXS * R);
     TAKE_D(eff, (size_t)R * N);
+    /* optional trailing section "TRN1": N x 6 transport data of the fit generator (not used by the chemistry port) */
+    if (len - (size_t)(p - m->copy) >= 8 && !memcmp(p, "TRN1", 4)) p += 8 + 8 * 6 * (size_t)N;
     if ((size_t)(p - m->copy) != len) { free(m->copy); free(m); return NULL; }
     m->has_eff = (int*)calloc(R, sizeof(int));
     for (int r = 0; r < R; ++r)
