@@ -84,7 +84,8 @@ def test_mock_caller_equals_ctypes_path(built, tmp_path, name):
     for mode, dt in (("scalar", deltaT), ("field", np.ascontiguousarray(g["dt"]))):
         cost = np.zeros(n)
         RR, Q = h.solve(T, p, rho, dt, Y, cost=cost)
-        Ynew = np.ascontiguousarray(Y + RR * (dt / rho)[None] if mode == "field" else Y + RR * (deltaT / rho)[None])
+        # same operation order as the C++ caller: Y += (RR * dt) / rho
+        Ynew = np.ascontiguousarray(Y + RR * (dt[None] if mode == "field" else deltaT) / rho[None])
         T2, psi, rho2, _, _ = h.correct_thermo(he, p, Ynew, T)
         _write_input(tmp_path / "in.bin", g, deltaT, rtol, atol)
         r = subprocess.run([built.MOCK, synth.blob_path(name), str(tmp_path / "in.bin"), str(tmp_path / f"out_{mode}.bin"), mode],
