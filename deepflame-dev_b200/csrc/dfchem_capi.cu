@@ -197,7 +197,9 @@ int launch_solve(dfchem_ctx* h, const SolveArgs& a, cudaStream_t s) {
     if (h->lpc_warps > 0) {
         const int per_cta = h->lpc_warps * kLpcLanes;
         const int grid = std::max(1, std::min(h->sm_count, (a.nC + per_cta - 1) / per_cta));
-        lpc_solve_kernel<<<grid, per_cta, lpc_smem_bytes(h), s>>>(h->lm, a, queue, cnt);
+#define CALL(NAP) lpc_solve_kernel<NAP><<<grid, per_cta, lpc_smem_bytes(h), s>>>(h->lm, a, queue, cnt)
+        DFC_DISPATCH_LPC(h->lm.NAP, CALL)
+#undef CALL
     } else {
 #define CALL(NP, NS) launch_solve_t<NP, NS>(h, a, queue, cnt, s)
         DFC_DISPATCH_NP(h->dm.NP, CALL)
@@ -269,28 +271,32 @@ int finish_create(dfchem_ctx* h, int device, dfchem_handle* out) {
     DFC_DISPATCH_NP(h->dm.NP, CALL)
 #undef CALL
     if (e != cudaSuccess) return bail("kernel configuration", e);
-    // Lane-per-cell solve kernel.  Measured on B200 (profiles/r2): 12x the warp-per-cell kernel on the one-step
-    // C7H16 mechanism (1.98e8 vs 1.65e7 cells/s), but no faster on the 16-21-reaction H2 mechanisms, where its
-    // serial shared-memory read-modify-write chains run at one warp per scheduler.  Default: global mechanisms
-    // with at most kLpcAutoReactions reactions; DFCHEM_SOLVER=lane / warp forces either kernel (A/B runs, tests).
+    // Lane-per-cell solve kernel (lane_cell.cuh, gather form).  Measured on B200 (profiles/r2/bench_*_1M_{lane2,warp}.json,
+    // 1,048,576 cells, rtol 1e-6 / atol 1e-10): c7_onestep 1.91e8 vs 1.65e7 cells/s (12x the warp-per-cell kernel), es80
+    // 5.58e6 vs 4.04e6 (1.4x), h2_li 1.29e6 vs 2.45e6 (slower: 8 active species need 2 KB of shared memory per lane, three
+    // warps per SM).  Default: mechanisms with at most 6 active species; DFCHEM_SOLVER=lane / warp forces either kernel.
     const char* solver_env = std::getenv("DFCHEM_SOLVER");
     const std::string solver = solver_env ? solver_env : "";
-    constexpr int kLpcAutoReactions = 6;
-    if (solver == "lane" || (solver != "warp" && h->mech.R <= kLpcAutoReactions)) {
+    constexpr int kLpcAutoActive = 6;
+    if (solver == "lane" || (solver != "warp" && h->dm.NA <= kLpcAutoActive)) {
         h->lpc = build_lpc_tables(h->mech, h->ht.perm, h->dm.NA);
         if (h->lpc.usable) {
             int max_optin = 0;
             if ((e = cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device)) != cudaSuccess)
                 return bail("cudaDeviceGetAttribute", e);
             const size_t per_warp = (size_t)kLpcLanes * h->lpc.layout.lane_doubles * sizeof(double);
-            const int warps = (int)std::min<size_t>(16, ((size_t)max_optin - h->lpc.blob.size()) / per_warp);
-            if (warps >= 2) {
+            const int max_w = h->lpc.layout.NAP <= 8 ? 8 : 4;   // the kernel's launch bounds (256 / 128 threads: 255 registers each)
+            const int warps = (int)std::min<size_t>(max_w, ((size_t)max_optin - h->lpc.blob.size()) / per_warp);
+            if (warps >= 1) {
                 if ((e = cudaMalloc(&h->d_lpc, h->lpc.blob.size())) != cudaSuccess) return bail("cudaMalloc(lpc tables)", e);
                 if ((e = cudaMemcpy(h->d_lpc, h->lpc.blob.data(), h->lpc.blob.size(), cudaMemcpyHostToDevice)) != cudaSuccess)
                     return bail("cudaMemcpy(lpc tables)", e);
                 h->lm = h->lpc.rebase(h->d_lpc);
-                if ((e = cudaFuncSetAttribute(lpc_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin)) != cudaSuccess)
-                    return bail("cudaFuncSetAttribute(lpc_solve_kernel)", e);
+                e = cudaErrorInvalidValue;
+#define CALL(NAP) e = cudaFuncSetAttribute(lpc_solve_kernel<NAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin)
+                DFC_DISPATCH_LPC(h->lpc.layout.NAP, CALL)
+#undef CALL
+                if (e != cudaSuccess) return bail("cudaFuncSetAttribute(lpc_solve_kernel)", e);
                 h->lpc_warps = warps;
             }
         }

@@ -70,7 +70,8 @@ solve_kernel(const DevMech mg, const SolveArgs a, unsigned int* queue, unsigned 
 // per-cell set-up (Arrhenius / equilibrium exponentials) is paid by many lanes at once and stiff cells
 // never hold back more than their own lane.
 constexpr int kLpcRefill = 8;
-__global__ void __launch_bounds__(512, 1)
+template <int NAP>
+__global__ void __launch_bounds__(NAP <= 8 ? 256 : 128, 1)
 lpc_solve_kernel(const LpcMech mg, const SolveArgs a, unsigned int* queue, unsigned long long* counters) {
     extern __shared__ double2 dfc_smem[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(dfc_smem);
@@ -97,15 +98,15 @@ lpc_solve_kernel(const LpcMech mg, const SolveArgs a, unsigned int* queue, unsig
             if (base + (unsigned)nidle >= (unsigned)a.nC) exhausted = true;  // this fetch reached the end of the batch
             if (S.cell < 0) {
                 const unsigned my = base + (unsigned)__popc(idle & ((1u << lane) - 1u));
-                if (my < (unsigned)a.nC) lpc_begin_cell(m, L, a, (int)my, S);
+                if (my < (unsigned)a.nC) lpc_begin_cell<NAP>(m, L, a, (int)my, S);
             }
         }
         if (__all_sync(0xffffffffu, S.cell < 0)) {
             if (exhausted) break;
             continue;
         }
-        if (S.cell >= 0 && lpc_attempt(m, L, S, a.rtol, a.atol, a.max_steps)) {
-            lpc_finish_cell(m, L, a, S);
+        if (S.cell >= 0 && lpc_attempt<NAP>(m, L, S, a.rtol, a.atol, a.max_steps)) {
+            lpc_finish_cell<NAP>(m, L, a, S);
             acc += S.acc;
             rej += S.rej;
             bad += S.status != kCellOk;

@@ -2,7 +2,11 @@
 // (src/dfChemistryModel/dfChemistryModel.C:738-780).  One lane owns one cell for its whole
 // integration; the lanes of a warp execute the same table entry on 32 different cells, so the
 // reaction decode is warp-uniform and every per-cell array lives in shared memory as
-// X[i * kLS + lane] (one bank per lane: conflict-free by construction).  Same ODE, same rate laws
+// X[i * kLS + lane] (one bank per lane: conflict-free by construction).  GATHER FORM: the reaction
+// loop only stores q_r and d q_r/d c_j; wdot_i, J_ij, the LU factors and the stage solves are loops
+// over COMPILE-TIME indices (template parameter NAP = padded active species), so their accumulators
+// and the matrix live in registers and shared memory sees loads and stores but no dependent
+// read-modify-write chain.  Same ODE, same rate laws
 // (SURVEY.md Appendix A), same RODAS4 scheme, controller and unstable-mode guard as the
 // warp-per-cell integrator (integrator.cuh); only the mapping differs.  No lane ever talks to
 // another lane, so the code is plain scalar C++ and compiles unchanged for the host emulation
@@ -28,51 +32,30 @@ struct LpcState {  // per-lane integrator state (registers)
     bool after_reject, need_base, first;
 };
 
-// RODAS4 coefficient tables as run-time indexable arrays (the stage loop is a real loop): constant memory on
-// the device (warp-uniform index), a local table in the host emulation
-#define LPC_RODAS_A                                                                                               \
-    {{0, 0, 0, 0, 0},                                                                                             \
-     {0.1544000000000000e+01, 0, 0, 0, 0},                                                                        \
-     {0.9466785280815826, 0.2557011698983284, 0, 0, 0},                                                           \
-     {0.3314825187068521e+01, 0.2896124015972201e+01, 0.9986419139977817, 0, 0},                                  \
-     {0.1221224509226641e+01, 0.6019134481288629e+01, 0.1253708332932087e+02, -0.6878860361058950, 0},            \
-     {0.1221224509226641e+01, 0.6019134481288629e+01, 0.1253708332932087e+02, -0.6878860361058950, 1.0}}
-#define LPC_RODAS_C                                                                                               \
-    {{0, 0, 0, 0, 0},                                                                                             \
-     {-0.5668800000000000e+01, 0, 0, 0, 0},                                                                       \
-     {-0.2430093356833875e+01, -0.2063599157091915, 0, 0, 0},                                                     \
-     {-0.1073529058151375, -0.9594562251023355e+01, -0.2047028614809616e+02, 0, 0},                               \
-     {0.7496443313967647e+01, -0.1024680431464352e+02, -0.3399990352819905e+02, 0.1170890893206160e+02, 0},       \
-     {0.8083246795921522e+01, -0.7981132988064893e+01, -0.3152159432874371e+02, 0.1631930543123136e+02,           \
-      -0.6058818238834054e+01}}
-#if defined(__CUDACC__)
-__constant__ double lpc_tab_a[6][5] = LPC_RODAS_A;
-__constant__ double lpc_tab_c[6][5] = LPC_RODAS_C;
-#endif
-DFC_HD double lpc_a(int i, int j) {
-#ifdef __CUDA_ARCH__
-    return lpc_tab_a[i][j];
-#else
-    constexpr double t[6][5] = LPC_RODAS_A;
-    return t[i][j];
-#endif
-}
-DFC_HD double lpc_c(int i, int j) {
-#ifdef __CUDA_ARCH__
-    return lpc_tab_c[i][j];
-#else
-    constexpr double t[6][5] = LPC_RODAS_C;
-    return t[i][j];
-#endif
-}
+// compile-time offsets (doubles per lane) of the fixed region
+template <int NAP>
+struct LpcFixed {
+    static constexpr int J = 0, LU = NAP * NAP, K = 2 * NAP * NAP, F0 = K + 6 * NAP, DC = F0 + NAP;
+};
 
 // LpcMech whose tables point into a copy of the blob at `nb` (shared memory)
 DFC_HD LpcMech lpc_rebase(const LpcMech& m, const uint8_t* nb) {
     LpcMech r = m;
 #define LPC_REBASE(field, T) r.field = reinterpret_cast<const T*>(nb + (reinterpret_cast<const uint8_t*>(m.field) - m.base))
-    LPC_REBASE(reac, LpcReaction);
+    LPC_REBASE(rx, LpcRx);
+    LPC_REBASE(powtab, double);
     LPC_REBASE(eff, double);
     LPC_REBASE(fall, double);
+    LPC_REBASE(arrh, double);
+    LPC_REBASE(fptr, int);
+    LPC_REBASE(fidx, int);
+    LPC_REBASE(fcoef, double);
+    LPC_REBASE(jptr, int);
+    LPC_REBASE(jidx, int);
+    LPC_REBASE(jcoef, double);
+    LPC_REBASE(gptr, int);
+    LPC_REBASE(gidx, int);
+    LPC_REBASE(gcoef, double);
     LPC_REBASE(W, double);
     LPC_REBASE(Tmid, double);
     LPC_REBASE(nasa, double);
@@ -84,8 +67,8 @@ DFC_HD LpcMech lpc_rebase(const LpcMech& m, const uint8_t* nb) {
 }
 
 // setState_TPY (dfChemistryModel.C:755): normalise Y, rho_ct = p Wbar/(R T), c_k = rho_ct Y_k / W_k
-DFC_HD void lpc_load_state(const LpcMech& m, double* L, const double* Y, int ldY, int cell, double T, double p,
-                           LpcState& S) {
+template <int NAP>
+DFC_HD void lpc_load_state(const LpcMech& m, double* L, const double* Y, int ldY, int cell, double T, double p, LpcState& S) {
     double s = 0.0;
     for (int k = 0; k < m.N; ++k) {
         const double y = Y[(size_t)m.perm[k] * ldY + cell];
@@ -101,7 +84,10 @@ DFC_HD void lpc_load_state(const LpcMech& m, double* L, const double* Y, int ldY
         LPC_AT(m.off_c, k) = ck;
         LPC_AT(m.off_cs, k) = ck;
     }
-    for (int i = 0; i < m.NA; ++i) LPC_AT(m.off_dc, i) = 0.0;
+    LPC_AT(m.off_c, m.N) = 1.0;   // the "absent factor" slot
+    LPC_AT(m.off_cs, m.N) = 1.0;
+    DFC_UNROLL
+    for (int i = 0; i < NAP; ++i) LPC_AT(LpcFixed<NAP>::DC, i) = 0.0;
     S.ysum = s;
     S.rho_ct = rho_ct;
 }
@@ -114,87 +100,99 @@ DFC_HD void lpc_setup(const LpcMech& m, double* L, double T) {
         const double* a = m.nasa + (size_t)k * 14 + (T <= m.Tmid[k] ? 0 : 7);
         const double h_RT = a[0] + T * (a[1] / 2 + T * (a[2] / 3 + T * (a[3] / 4 + T * a[4] / 5))) + a[5] / T;
         const double s_R = a[0] * logT + T * (a[1] + T * (a[2] / 2 + T * (a[3] / 3 + T * a[4] / 4))) + a[6];
-        LPC_AT(m.off_x, k) = h_RT - s_R;
+        LPC_AT(m.off_q, k) = h_RT - s_R;
     }
     const double log_c0 = log(kOneAtm / (kGasConstant * T));
     for (int r = 0; r < m.R; ++r) {
-        const LpcReaction& x = m.reac[r];
-        const double lnk = x.lnA + x.b * logT - x.Ta * rT;
+        const LpcRx x = m.rx[r];
+        const double* ar = m.arrh + (size_t)r * 3;
+        const double lnk = ar[0] + ar[1] * logT - ar[2] * rT;
         double rk = 0.0;
-        if (x.rev) {
+        if (x.x & 4u) {
             double dG = 0.0, dn = 0.0;
-            for (int n = 0; n < x.nnet; ++n) {
-                dG = fma(x.nnu[n], LPC_AT(m.off_x, x.nsp[n]), dG);
-                dn += x.nnu[n];
+            for (int e = m.gptr[r]; e < m.gptr[r + 1]; ++e) {
+                dG = fma(m.gcoef[e], LPC_AT(m.off_q, m.gidx[e]), dG);
+                dn += m.gcoef[e];
             }
             rk = fmin(exp(dG - dn * log_c0), kBig);
         }
         LPC_AT(m.off_kf, r) = exp(lnk);
         LPC_AT(m.off_rkc, r) = rk;
-        if (x.fall >= 0) {
-            const double* f = m.fall + (size_t)x.fall * 8;
-            LPC_AT(m.off_k0, x.fall) = fmin(exp(f[0] + f[1] * logT - f[2] * rT - lnk), 1e200);
+        if ((x.x & 3u) >= (uint32_t)kFalloffLindemann) {
+            const int fid = (int)(x.z & 0xFFu);
+            const double* f = m.fall + (size_t)fid * 8;
+            LPC_AT(m.off_k0, fid) = fmin(exp(f[0] + f[1] * logT - f[2] * rT - lnk), 1e200);
             double lf = 0.0;
             if (f[7] != 0.0) {
                 double fc = (1.0 - f[3]) * exp(-T / f[4]) + f[3] * exp(-T / f[5]);
                 if (f[6] < 1e299) fc += exp(-f[6] / T);
                 lf = log10(fmax(fc, kSmall));
             }
-            LPC_AT(m.off_lfc, x.fall) = lf;
+            LPC_AT(m.off_lfc, fid) = lf;
         }
     }
 }
 
-DFC_HD D2 lpc_factor(bool simple, double o, double c) {
-    if (simple) {
-        if (o == 1.0) return D2{c, 1.0};
-        if (o == 2.0) return D2{c * c, 2.0 * c};
-        return D2{c * c * c, 3.0 * c * c};
-    }
-    return pow_factor(o, c);
-}
-
-// f = wdot(cx) [and J = d wdot / d c, dense NA x NA row-major]; q_out (optional): net rates of progress
+// Reaction loop: q_r -> column off_q (and, if JAC, the partial derivatives -> column off_dq).  Stores only.
 template <bool JAC>
-DFC_HD void lpc_eval(const LpcMech& m, double* L, int off_cx, double* q_out = nullptr, size_t ldq = 0) {
-    const int NA = m.NA, N = m.N;
-    for (int i = 0; i < NA; ++i) LPC_AT(m.off_f, i) = 0.0;
-    if (JAC)
-        for (int e = 0; e < NA * NA; ++e) LPC_AT(m.off_J, e) = 0.0;
+DFC_HD void lpc_reactions(const LpcMech& m, double* L, int off_cx, double* qf_out = nullptr, double* qr_out = nullptr,
+                          size_t ldq = 0) {
+    const uint32_t none = (uint32_t)m.N;
     DFC_NOUNROLL
     for (int r = 0; r < m.R; ++r) {
-        const LpcReaction& x = m.reac[r];
-        double fv[3] = {1.0, 1.0, 1.0}, fd[3] = {0.0, 0.0, 0.0}, pv[3] = {1.0, 1.0, 1.0}, pd[3] = {0.0, 0.0, 0.0};
-        const bool simple = x.simple != 0;
-        DFC_UNROLL
-        for (int a = 0; a < 3; ++a) {
-            if (a < x.nr) {
-                const D2 t = lpc_factor(simple, x.rord[a], LPC_AT(off_cx, x.rsp[a]));
-                fv[a] = t.x;
-                fd[a] = t.y;
+        const LpcRx x = m.rx[r];
+        const uint32_t kind = x.x & 3u;
+        const uint32_t fo[3] = {(x.x >> 8) & 63u, (x.x >> 14) & 63u, (x.x >> 20) & 63u};
+        const uint32_t po[3] = {x.y & 63u, (x.y >> 6) & 63u, (x.y >> 12) & 63u};
+        double fv[3], fd[3], pv[3], pd[3];
+        if (!(x.x & 8u)) {
+            DFC_UNROLL
+            for (int a = 0; a < 3; ++a) {
+                fv[a] = LPC_AT(off_cx, fo[a]);
+                pv[a] = LPC_AT(off_cx, po[a]);
+                fd[a] = 1.0;
+                pd[a] = 1.0;
             }
-            if (a < x.np) {
-                const D2 t = lpc_factor(simple, x.pord[a], LPC_AT(off_cx, x.psp[a]));
-                pv[a] = t.x;
-                pd[a] = t.y;
+        } else {  // fractional / large orders: c^o with Cantera's rule (non-positive c -> 0)
+            const double* pw = m.powtab + (size_t)((x.z >> 8) & 0xFFu) * 9;
+            for (int a = 0; a < 3; ++a) {
+                fv[a] = pv[a] = 1.0;
+                fd[a] = pd[a] = 0.0;
+                if (fo[a] != none) {
+                    const D2 t = pow_factor(pw[a], LPC_AT(off_cx, fo[a]));
+                    fv[a] = t.x;
+                    fd[a] = t.y;
+                }
+                if (po[a] != none) {
+                    const D2 t = pow_factor(pw[6 + a], LPC_AT(off_cx, po[a]));
+                    pv[a] = t.x;
+                    pd[a] = t.y;
+                }
             }
         }
         double kfe = LPC_AT(m.off_kf, r);
         const double rkc = LPC_AT(m.off_rkc, r);
         double dkdM = 0.0;
-        if (x.kind != kElementary) {
-            const double* ef = m.eff + (size_t)x.mset * N;
-            double M = 0.0;
-            for (int k = 0; k < N; ++k) M = fma(ef[k], LPC_AT(off_cx, k), M);
-            if (x.kind == kThreeBody) {
+        if (kind != (uint32_t)kElementary) {
+            const double* ef = m.eff + (size_t)(x.y >> 20) * m.N;
+            double M0 = 0.0, M1 = 0.0;
+            int k = 0;
+            for (; k + 1 < m.N; k += 2) {
+                M0 = fma(ef[k], LPC_AT(off_cx, k), M0);
+                M1 = fma(ef[k + 1], LPC_AT(off_cx, k + 1), M1);
+            }
+            if (k < m.N) M0 = fma(ef[k], LPC_AT(off_cx, k), M0);
+            const double M = M0 + M1;
+            if (kind == (uint32_t)kThreeBody) {
                 dkdM = kfe;
                 kfe *= M;
             } else {
-                const double rk = LPC_AT(m.off_k0, x.fall);  // k0 / kinf
+                const int fid = (int)(x.z & 0xFFu);
+                const double rk = LPC_AT(m.off_k0, fid);  // k0 / kinf
                 const double pr = M * rk;
                 double F = 1.0, dF_dpr = 0.0;
-                if (x.kind == kFalloffTroe) {
-                    const double lf = LPC_AT(m.off_lfc, x.fall);
+                if (kind == (uint32_t)kFalloffTroe) {
+                    const double lf = LPC_AT(m.off_lfc, fid);
                     const double lpr = log10(fmax(pr, kSmall));
                     const double cc = -0.4 - 0.67 * lf;
                     const double nn = 0.75 - 1.27 * lf;
@@ -213,85 +211,110 @@ DFC_HD void lpc_eval(const LpcMech& m, double* L, int off_cx, double* q_out = nu
         const double Pf = fv[0] * fv[1] * fv[2];
         const double Pp = pv[0] * pv[1] * pv[2];
         const double kre = kfe * rkc;
-        const double q = kfe * Pf - kre * Pp;
-        if (q_out) q_out[(size_t)x.caller_index * ldq] = q;
-        DFC_UNROLL
-        for (int n = 0; n < kLpcMaxNet; ++n)
-            if (n < x.nnet) LPC_AT(m.off_f, x.nsp[n]) = fma(x.nnu[n], q, LPC_AT(m.off_f, x.nsp[n]));
+        LPC_AT(m.off_q, r) = kfe * Pf - kre * Pp;
+        if (qf_out) {
+            const size_t o = (size_t)(x.z >> 16) * ldq;
+            qf_out[o] = kfe * Pf;
+            qr_out[o] = kre * Pp;
+        }
         if (JAC) {
-            DFC_UNROLL
-            for (int a = 0; a < 3; ++a) {
-                if (a < x.nr && x.rsp[a] < NA) {
-                    const double d = kfe * fd[a] * (a == 0 ? fv[1] * fv[2] : a == 1 ? fv[0] * fv[2] : fv[0] * fv[1]);
-                    for (int n = 0; n < x.nnet; ++n) {
-                        const int e = x.nsp[n] * NA + x.rsp[a];
-                        LPC_AT(m.off_J, e) = fma(x.nnu[n], d, LPC_AT(m.off_J, e));
-                    }
-                }
-                if (a < x.np && x.psp[a] < NA) {
-                    const double d = -kre * pd[a] * (a == 0 ? pv[1] * pv[2] : a == 1 ? pv[0] * pv[2] : pv[0] * pv[1]);
-                    for (int n = 0; n < x.nnet; ++n) {
-                        const int e = x.nsp[n] * NA + x.psp[a];
-                        LPC_AT(m.off_J, e) = fma(x.nnu[n], d, LPC_AT(m.off_J, e));
-                    }
-                }
-            }
-            if (x.kind != kElementary) {
-                const double dM = dkdM * (Pf - rkc * Pp);
-                const double* ef = m.eff + (size_t)x.mset * N;
-                for (int j = 0; j < NA; ++j) {
-                    const double w = dM * ef[j];
-                    if (ef[j] != 0.0)
-                        for (int n = 0; n < x.nnet; ++n) {
-                            const int e = x.nsp[n] * NA + j;
-                            LPC_AT(m.off_J, e) = fma(x.nnu[n], w, LPC_AT(m.off_J, e));
-                        }
-                }
-            }
+            int slot = m.off_dq + (int)x.w;
+            if (fo[0] != none) LPC_AT(slot++, 0) = kfe * fd[0] * fv[1] * fv[2];
+            if (fo[1] != none) LPC_AT(slot++, 0) = kfe * fv[0] * fd[1] * fv[2];
+            if (fo[2] != none) LPC_AT(slot++, 0) = kfe * fv[0] * fv[1] * fd[2];
+            if (po[0] != none) LPC_AT(slot++, 0) = -kre * pd[0] * pv[1] * pv[2];
+            if (po[1] != none) LPC_AT(slot++, 0) = -kre * pv[0] * pd[1] * pv[2];
+            if (po[2] != none) LPC_AT(slot++, 0) = -kre * pv[0] * pv[1] * pd[2];
+            if (kind != (uint32_t)kElementary) LPC_AT(slot, 0) = dkdM * (Pf - rkc * Pp);
         }
     }
 }
 
-// A = I/(h g) - J, LU in place without pivoting (1/pivot stored on the diagonal).  Returns the number
-// of negative pivots (unstable-mode guard, integrator.cuh).
-DFC_HD int lpc_factor_matrix(const LpcMech& m, double* L, double inv_hg) {
-    const int NA = m.NA;
-    for (int i = 0; i < NA; ++i)
-        for (int j = 0; j < NA; ++j) LPC_AT(m.off_A, i * NA + j) = (i == j ? inv_hg : 0.0) - LPC_AT(m.off_J, i * NA + j);
-    int neg = 0;
-    for (int k = 0; k < NA; ++k) {
-        const double p = 1.0 / LPC_AT(m.off_A, k * NA + k);
-        LPC_AT(m.off_A, k * NA + k) = p;
-        neg += p < 0.0 ? 1 : 0;
-        for (int i = k + 1; i < NA; ++i) {
-            const double l = LPC_AT(m.off_A, i * NA + k) * p;
-            LPC_AT(m.off_A, i * NA + k) = l;
-            for (int j = k + 1; j < NA; ++j)
-                LPC_AT(m.off_A, i * NA + j) = fma(-l, LPC_AT(m.off_A, k * NA + j), LPC_AT(m.off_A, i * NA + j));
+// f[i] = wdot_i(cx) in registers; if JAC also J (dense NAP x NAP, row-major, fixed region) from the derivative column
+template <int NAP, bool JAC>
+DFC_HD void lpc_eval(const LpcMech& m, double* L, int off_cx, double (&f)[NAP]) {
+    lpc_reactions<JAC>(m, L, off_cx);
+    DFC_UNROLL
+    for (int i = 0; i < NAP; ++i) {
+        double a0 = 0.0, a1 = 0.0;
+        int e = m.fptr[i];
+        const int e1 = m.fptr[i + 1];
+        for (; e + 1 < e1; e += 2) {
+            a0 = fma(m.fcoef[e], LPC_AT(m.off_q, m.fidx[e]), a0);
+            a1 = fma(m.fcoef[e + 1], LPC_AT(m.off_q, m.fidx[e + 1]), a1);
         }
+        if (e < e1) a0 = fma(m.fcoef[e], LPC_AT(m.off_q, m.fidx[e]), a0);
+        f[i] = a0 + a1;
+    }
+    if (JAC) {
+        DFC_UNROLL
+        for (int ij = 0; ij < NAP * NAP; ++ij) {
+            double a0 = 0.0, a1 = 0.0;
+            int e = m.jptr[ij];
+            const int e1 = m.jptr[ij + 1];
+            for (; e + 1 < e1; e += 2) {
+                a0 = fma(m.jcoef[e], LPC_AT(m.off_dq, m.jidx[e]), a0);
+                a1 = fma(m.jcoef[e + 1], LPC_AT(m.off_dq, m.jidx[e + 1]), a1);
+            }
+            if (e < e1) a0 = fma(m.jcoef[e], LPC_AT(m.off_dq, m.jidx[e]), a0);
+            LPC_AT(LpcFixed<NAP>::J, ij) = a0 + a1;
+        }
+    }
+}
+
+// A = I/(h g) - J, LU in registers without pivoting (1/pivot stored on the diagonal), factors -> fixed region.
+// Returns the number of negative pivots (unstable-mode guard, integrator.cuh).
+template <int NAP>
+DFC_HD int lpc_factor_matrix(double* L, double inv_hg) {
+    double A[NAP][NAP];
+    DFC_UNROLL
+    for (int i = 0; i < NAP; ++i) {
+        DFC_UNROLL
+        for (int j = 0; j < NAP; ++j) A[i][j] = (i == j ? inv_hg : 0.0) - LPC_AT(LpcFixed<NAP>::J, i * NAP + j);
+    }
+    int neg = 0;
+    DFC_UNROLL
+    for (int k = 0; k < NAP; ++k) {
+        const double p = 1.0 / A[k][k];
+        A[k][k] = p;
+        neg += p < 0.0 ? 1 : 0;
+        DFC_UNROLL
+        for (int i = k + 1; i < NAP; ++i) {
+            const double l = A[i][k] * p;
+            A[i][k] = l;
+            DFC_UNROLL
+            for (int j = k + 1; j < NAP; ++j) A[i][j] = fma(-l, A[k][j], A[i][j]);
+        }
+    }
+    DFC_UNROLL
+    for (int i = 0; i < NAP; ++i) {
+        DFC_UNROLL
+        for (int j = 0; j < NAP; ++j) LPC_AT(LpcFixed<NAP>::LU, i * NAP + j) = A[i][j];
     }
     return neg;
 }
-// x <- A^-1 x (x = the off_x array)
-DFC_HD void lpc_lu_solve(const LpcMech& m, double* L) {
-    const int NA = m.NA;
-    for (int i = 1; i < NA; ++i) {
-        double s = LPC_AT(m.off_x, i);
-        for (int j = 0; j < i; ++j) s = fma(-LPC_AT(m.off_A, i * NA + j), LPC_AT(m.off_x, j), s);
-        LPC_AT(m.off_x, i) = s;
+// x <- A^-1 x, x in registers, factors read at compile-time offsets
+template <int NAP>
+DFC_HD void lpc_lu_solve(const double* L, double (&x)[NAP]) {
+    DFC_UNROLL
+    for (int i = 1; i < NAP; ++i) {
+        DFC_UNROLL
+        for (int j = 0; j < i; ++j) x[i] = fma(-LPC_AT(LpcFixed<NAP>::LU, i * NAP + j), x[j], x[i]);
     }
-    for (int i = NA - 1; i >= 0; --i) {
-        double s = LPC_AT(m.off_x, i);
-        for (int j = i + 1; j < NA; ++j) s = fma(-LPC_AT(m.off_A, i * NA + j), LPC_AT(m.off_x, j), s);
-        LPC_AT(m.off_x, i) = s * LPC_AT(m.off_A, i * NA + i);
+    DFC_UNROLL
+    for (int i = NAP - 1; i >= 0; --i) {
+        DFC_UNROLL
+        for (int j = i + 1; j < NAP; ++j) x[i] = fma(-LPC_AT(LpcFixed<NAP>::LU, i * NAP + j), x[j], x[i]);
+        x[i] *= LPC_AT(LpcFixed<NAP>::LU, i * NAP + i);
     }
 }
 
+template <int NAP>
 DFC_HD void lpc_begin_cell(const LpcMech& m, double* L, const SolveArgs& a, int cell, LpcState& S) {
     const double T = a.T[cell];
     S.cell = cell;
     S.dt = a.dt ? a.dt[cell] : a.dt_uniform;
-    lpc_load_state(m, L, a.Y, a.ldY, cell, T, a.p[cell], S);
+    lpc_load_state<NAP>(m, L, a.Y, a.ldY, cell, T, a.p[cell], S);
     lpc_setup(m, L, T);
     S.t = 0.0;
     S.h = S.dt;
@@ -307,23 +330,57 @@ DFC_HD void lpc_begin_cell(const LpcMech& m, double* L, const SolveArgs& a, int 
     }
 }
 
+// stage I of RODAS4 with I a compile-time constant: stage point, rate evaluation, right-hand side, solve
+template <int NAP, int I>
+DFC_HD void lpc_stage(const LpcMech& m, double* L, double ih) {
+    using F = LpcFixed<NAP>;
+    double x[NAP];
+    if (I == 0) {
+        DFC_UNROLL
+        for (int row = 0; row < NAP; ++row) x[row] = LPC_AT(F::F0, row);
+    } else {
+        DFC_UNROLL
+        for (int row = 0; row < NAP; ++row) {
+            double v = LPC_AT(m.off_c, row);
+            DFC_UNROLL
+            for (int j = 0; j < I; ++j)
+                if (rodas_a(I, j) != 0.0) v = fma(rodas_a(I, j), LPC_AT(F::K, j * NAP + row), v);
+            if (row < m.NA) LPC_AT(m.off_cs, row) = v;
+        }
+        lpc_eval<NAP, false>(m, L, m.off_cs, x);
+        DFC_UNROLL
+        for (int row = 0; row < NAP; ++row) {
+            DFC_UNROLL
+            for (int j = 0; j < I; ++j) x[row] = fma(rodas_c(I, j) * ih, LPC_AT(F::K, j * NAP + row), x[row]);
+        }
+    }
+    lpc_lu_solve<NAP>(L, x);
+    DFC_UNROLL
+    for (int row = 0; row < NAP; ++row) LPC_AT(F::K, I * NAP + row) = x[row];
+}
+
 // One step attempt of the cell on this lane (the body of integrate_cell's loops).  Returns true
 // when the sub-step is complete (or has failed: S.status).
+template <int NAP>
 DFC_HD bool lpc_attempt(const LpcMech& m, double* L, LpcState& S, double rtol, double atol, int max_steps) {
-    const int NA = m.NA;
+    using F = LpcFixed<NAP>;
     const double atol_rho = atol * S.rho_ct;
     if (!(S.dt > 0.0)) return true;
     if (S.need_base) {
-        lpc_eval<true>(m, L, m.off_c);
-        for (int i = 0; i < NA; ++i) LPC_AT(m.off_f0, i) = LPC_AT(m.off_f, i);
+        double f0[NAP];
+        lpc_eval<NAP, true>(m, L, m.off_c, f0);
+        DFC_UNROLL
+        for (int i = 0; i < NAP; ++i) LPC_AT(F::F0, i) = f0[i];
         S.need_base = false;
         if (S.first) {
             double e2 = 0.0;
-            for (int i = 0; i < NA; ++i) {
-                const double sc = atol_rho / m.W[i] + rtol * fabs(LPC_AT(m.off_c, i));
-                const double e = LPC_AT(m.off_f0, i) / sc;
-                e2 = fma(e, e, e2);
-            }
+            DFC_UNROLL
+            for (int i = 0; i < NAP; ++i)
+                if (i < m.NA) {
+                    const double sc = atol_rho / m.W[i] + rtol * fabs(LPC_AT(m.off_c, i));
+                    const double e = f0[i] / sc;
+                    e2 = fma(e, e, e2);
+                }
             const double d1 = sqrt(e2 / (double)m.N);
             if (d1 * S.dt > DFC_H0K) S.h = fmax(DFC_H0K / d1, 1e-3 * S.dt);
             S.first = false;
@@ -340,66 +397,63 @@ DFC_HD bool lpc_attempt(const LpcMech& m, double* L, LpcState& S, double rtol, d
     }
     const bool cut = hs < S.h;
     const double ih = 1.0 / hs;
-    if (lpc_factor_matrix(m, L, ih / kGamma) & 1) {  // unstable-mode guard
+    if (lpc_factor_matrix<NAP>(L, ih / kGamma) & 1) {  // unstable-mode guard
         ++S.rej;
         S.after_reject = true;
         S.h = hs * kFacUnstable;
         return false;
     }
-    DFC_NOUNROLL
-    for (int i = 0; i < kStages; ++i) {
-        if (i > 0) {
-            for (int row = 0; row < NA; ++row) {
-                double v = LPC_AT(m.off_c, row);
-                for (int j = 0; j < i; ++j) v = fma(lpc_a(i, j), LPC_AT(m.off_k, j * NA + row), v);
-                LPC_AT(m.off_cs, row) = v;
-            }
-            lpc_eval<false>(m, L, m.off_cs);
-        }
-        for (int row = 0; row < NA; ++row) {
-            double v = i == 0 ? LPC_AT(m.off_f0, row) : LPC_AT(m.off_f, row);
-            for (int j = 0; j < i; ++j) v = fma(lpc_c(i, j) * ih, LPC_AT(m.off_k, j * NA + row), v);
-            LPC_AT(m.off_x, row) = v;
-        }
-        lpc_lu_solve(m, L);
-        for (int row = 0; row < NA; ++row) LPC_AT(m.off_k, i * NA + row) = LPC_AT(m.off_x, row);
-    }
-    // new solution = argument of the last stage + k_6; error estimate = k_6.  The increment is left in off_x.
+    lpc_stage<NAP, 0>(m, L, ih);
+    lpc_stage<NAP, 1>(m, L, ih);
+    lpc_stage<NAP, 2>(m, L, ih);
+    lpc_stage<NAP, 3>(m, L, ih);
+    lpc_stage<NAP, 4>(m, L, ih);
+    lpc_stage<NAP, 5>(m, L, ih);
+    // new solution = argument of the last stage + k_6; error estimate = k_6
+    double inc[NAP];
     double e2 = 0.0;
-    for (int row = 0; row < NA; ++row) {
-        double inc = LPC_AT(m.off_k, 5 * NA + row);
-        for (int j = 0; j < 5; ++j) inc = fma(lpc_a(5, j), LPC_AT(m.off_k, j * NA + row), inc);
-        LPC_AT(m.off_x, row) = inc;
-        const double c0 = LPC_AT(m.off_c, row);
-        const double sc = atol_rho / m.W[row] + rtol * fmax(fabs(c0), fabs(c0 + inc));
-        const double e = LPC_AT(m.off_k, 5 * NA + row) / sc;
-        e2 = fma(e, e, e2);
+    DFC_UNROLL
+    for (int row = 0; row < NAP; ++row) {
+        const double k6 = LPC_AT(F::K, 5 * NAP + row);
+        double v = k6;
+        DFC_UNROLL
+        for (int j = 0; j < 5; ++j) v = fma(rodas_a(5, j), LPC_AT(F::K, j * NAP + row), v);
+        inc[row] = v;
+        if (row < m.NA) {
+            const double c0 = LPC_AT(m.off_c, row);
+            const double sc = atol_rho / m.W[row] + rtol * fmax(fabs(c0), fabs(c0 + v));
+            const double e = k6 / sc;
+            e2 = fma(e, e, e2);
+        }
     }
     double en = sqrt(e2 / (double)m.N);
     if (!(en < 1e30)) en = 1e30;
     double fac = kFacSafe / sqrt(sqrt(fmax(en, 1e-12)));
-    if (en <= 1.0) {
+    const bool accepted = en <= 1.0;
+    if (accepted) {
         fac = fmin(fmax(fac, kFacMin), S.after_reject ? 1.0 : kFacMax);
         S.after_reject = false;
         ++S.acc;
         S.t += hs;
-        for (int row = 0; row < NA; ++row) {
-            const double inc = LPC_AT(m.off_x, row);
-            LPC_AT(m.off_dc, row) += inc;
-            LPC_AT(m.off_c, row) += inc;
-        }
+        DFC_UNROLL
+        for (int row = 0; row < NAP; ++row)
+            if (row < m.NA) {
+                LPC_AT(F::DC, row) += inc[row];
+                LPC_AT(m.off_c, row) += inc[row];
+            }
         S.need_base = true;
     } else {
         fac = fmin(fmax(fac, kFacMinReject), 1.0);
         ++S.rej;
         S.after_reject = true;
     }
-    S.h_free = (S.need_base && cut) ? fmax(S.h, hs * fac) : hs * fac;
+    S.h_free = (accepted && cut) ? fmax(S.h, hs * fac) : hs * fac;
     S.h = hs * fac;
     return S.t >= S.dt * (1.0 - 1e-14);
 }
 
 // RR_i = (Ynew_i - Yraw_i)/dt * rho_OF against the RAW Y, Qdot = -sum hc_i RR_i (dfChemistryModel.C:768-772)
+template <int NAP>
 DFC_HD void lpc_finish_cell(const LpcMech& m, double* L, const SolveArgs& a, const LpcState& S) {
     const int cell = S.cell;
     const double scale = S.dt > 0.0 ? a.rho[cell] / S.dt : 0.0;
@@ -409,7 +463,7 @@ DFC_HD void lpc_finish_cell(const LpcMech& m, double* L, const SolveArgs& a, con
         const int ko = m.perm[k];
         const double yraw = a.Y[(size_t)ko * a.ldY + cell];
         double dY = yraw * rys - yraw;
-        if (k < m.NA) dY += LPC_AT(m.off_dc, k) * m.W[k] / S.rho_ct;
+        if (k < m.NA) dY += LPC_AT(LpcFixed<NAP>::DC, k) * m.W[k] / S.rho_ct;
         const double rr = dY * scale;
         a.RR[(size_t)ko * a.ldRR + cell] = rr;
         qd = fma(-m.hc[k], rr, qd);
@@ -419,5 +473,15 @@ DFC_HD void lpc_finish_cell(const LpcMech& m, double* L, const SolveArgs& a, con
     if (a.status) a.status[cell] = S.status;
     if (a.dtchem && S.dt > 0.0 && S.status == kCellOk) a.dtchem[cell] = S.h_free;
 }
+
+// instantiation list of the padded sizes (lpc_pad)
+#define DFC_DISPATCH_LPC(NAP_VALUE, CALL) \
+    switch (NAP_VALUE) {                  \
+        case 4: CALL(4); break;           \
+        case 6: CALL(6); break;           \
+        case 8: CALL(8); break;           \
+        case 12: CALL(12); break;         \
+        default: break;                   \
+    }
 
 }  // namespace dfchem

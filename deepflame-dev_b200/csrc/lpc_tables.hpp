@@ -4,6 +4,12 @@
 // lanes of a warp walk the SAME table entry at the same time, so every table read is a broadcast
 // and the decode is paid once per 32 cells.  Second output of the host mechanism compiler next to
 // dev_tables.hpp; the rate laws are the same (Cantera 2.6 GasKinetics).
+//
+// GATHER FORM (round 2, second version): the reaction loop only STORES (q_r and the partial
+// derivatives d q_r / d c_j go to per-lane shared-memory columns); wdot_i and J_ij are then summed
+// from per-target entry lists in loops whose TARGET index is a compile-time constant (the kernel is
+// templated on the padded species count), so the accumulators live in registers and no shared-memory
+// read-modify-write chain exists anywhere.
 #pragma once
 #include <cstdint>
 #include <vector>
@@ -13,40 +19,44 @@
 namespace dfchem {
 
 constexpr int kLpcMaxActive = 12;    // mechanisms with more active species use the warp-per-cell kernels
-constexpr int kLpcMaxNet = 2 * kMaxSide;
+constexpr int kLpcMaxSpecies = 60;   // species indices are 6-bit fields of the reaction record (index N = "one")
 
-// One reaction, read uniformly by the warp (all fields in internal species numbering, active first).
-struct LpcReaction {
-    int32_t kind;               // ReactionKind
-    int32_t rev;                // reversible
-    int32_t nr, np;             // concentration factors on the forward / reverse side
-    int32_t rsp[kMaxSide];      // forward factors: species
-    int32_t psp[kMaxSide];      // reverse factors: species (reversible reactions only)
-    int32_t simple;             // every order is 1, 2 or 3 (no pow() needed)
-    int32_t mset;               // third-body efficiency set (-1: none)
-    int32_t fall;               // falloff record (-1: none)
-    int32_t nnet;               // species with non-zero net stoichiometric coefficient
-    int32_t nsp[kLpcMaxNet];    // ... their indices (all < NA)
-    int32_t caller_index;       // index in the Mechanism record (rates-of-progress output order)
-    int32_t pad_;
-    double rord[kMaxSide];      // forward orders (the `orders` entry, else the stoichiometric coefficient)
-    double pord[kMaxSide];      // reverse orders = product stoichiometric coefficients
-    double nnu[kLpcMaxNet];     // net stoichiometric coefficients nu'' - nu'
-    double lnA, b, Ta;          // k = exp(lnA + b ln T - Ta/T)   (high-pressure limit for falloff)
+// Reaction record, 16 bytes, read uniformly by the warp.  A side holds up to 3 concentration factors; an
+// integer order nu is expanded into nu repeated factors; an absent factor is the index N, whose concentration
+// slot holds 1.0.  Reactions that do not fit (fractional orders, more than 3 factors) use the pow path:
+// factors = distinct species, powtab[pow_id*9 + {0..2 forward order, 3..5 unused, 6..8 reverse order}].
+//   x = kind | rev<<2 | pow<<3 | rf0<<8 | rf1<<14 | rf2<<20
+//   y = pf0 | pf1<<6 | pf2<<12 | mset<<20            (mset 0xFF: none)
+//   z = fall_id | pow_id<<8 | caller_index<<16
+//   w = dq_off   first slot of this reaction in the per-lane derivative column; slot order: present reactant
+//                factors, present product factors (reversible only), d q/d[M] (three-body / falloff only)
+struct LpcRx {
+    uint32_t x, y, z, w;
 };
 
 // Device/host view.  Per-lane arrays live in shared memory as X[i * LS + lane] (LS = 32 on the
-// device, 1 in the host emulation); offsets below are in doubles per lane.
+// device, 1 in the host emulation); offsets below are in doubles per lane.  The arrays whose size depends on
+// the padded active-species count only come first, at compile-time offsets (lane_cell.cuh: LpcFixed<NAP>).
 struct LpcMech {
-    int N, NA, R, n_msets, n_fall;
-    int off_c, off_cs, off_kf, off_rkc, off_k0, off_lfc, off_f, off_J, off_A, off_k, off_f0, off_dc, off_x,
-        lane_doubles;
+    int N, NA, NAP, R, n_msets, n_fall, n_dq;
+    int off_c, off_cs, off_kf, off_rkc, off_k0, off_lfc, off_q, off_dq, lane_doubles;
     // tables (one contiguous blob; staged into shared memory by every CTA)
     const uint8_t* base;
     int bytes;
-    const LpcReaction* reac;   // [R]
+    const LpcRx* rx;           // [R]
+    const double* powtab;      // [n_pow * 9]
     const double* eff;         // [n_msets * N] dense efficiencies, internal order
     const double* fall;        // [n_fall * 8] ln A0, b0, Ta0, Troe A, T3, T1, T2, is_troe
+    const double* arrh;        // [R * 3] ln A, b, Ta
+    const int* fptr;           // [NAP + 1] wdot gather lists: entries fidx (reaction), fcoef (nu)
+    const int* fidx;
+    const double* fcoef;
+    const int* jptr;           // [NAP*NAP + 1] Jacobian gather lists: entries jidx (dq slot), jcoef
+    const int* jidx;
+    const double* jcoef;
+    const int* gptr;           // [R + 1] equilibrium-constant lists: entries gidx (species), gcoef (net nu)
+    const int* gidx;
+    const double* gcoef;
     const double* W;           // [N]
     const double* Tmid;        // [N]
     const double* nasa;        // [N * 14]
@@ -60,6 +70,10 @@ struct HostLpc {
     std::vector<uint8_t> blob;
     LpcMech rebase(const void* base) const;
 };
+
+constexpr int lpc_pad(int NA) { return NA <= 4 ? 4 : NA <= 6 ? 6 : NA <= 8 ? 8 : 12; }
+// per-lane doubles of the fixed region: J, LU, six stage vectors, f0, dc
+constexpr int lpc_fixed_doubles(int NAP) { return 2 * NAP * NAP + 8 * NAP; }
 
 // perm: internal -> caller species index with the NA active species first (HostTables::perm)
 HostLpc build_lpc_tables(const Mechanism& m, const std::vector<int>& perm, int NA);

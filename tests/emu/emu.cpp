@@ -173,17 +173,20 @@ int emu_solve_lpc(void* h, int nC, const double* T, const double* p, const doubl
     SolveArgs a{nC, T, p, rho, dt, dt_uniform, Y, ldY, RR, ldRR, Qdot, cost, status, rtol, atol, max_steps};
     counters[0] = counters[1] = counters[2] = 0;
     std::vector<double> L(m.lane_doubles);
-    for (int cell = 0; cell < nC; ++cell) {
-        std::fill(L.begin(), L.end(), std::numeric_limits<double>::quiet_NaN());
-        LpcState S;
-        lpc_begin_cell(m, L.data(), a, cell, S);
-        while (!lpc_attempt(m, L.data(), S, rtol, atol, max_steps)) {
-        }
-        lpc_finish_cell(m, L.data(), a, S);
-        counters[0] += S.acc;
-        counters[1] += S.rej;
-        counters[2] += S.status != 0;
+#define CALL(NAP)                                                              \
+    for (int cell = 0; cell < nC; ++cell) {                                    \
+        std::fill(L.begin(), L.end(), std::numeric_limits<double>::quiet_NaN()); \
+        LpcState S;                                                            \
+        lpc_begin_cell<NAP>(m, L.data(), a, cell, S);                          \
+        while (!lpc_attempt<NAP>(m, L.data(), S, rtol, atol, max_steps)) {     \
+        }                                                                      \
+        lpc_finish_cell<NAP>(m, L.data(), a, S);                               \
+        counters[0] += S.acc;                                                  \
+        counters[1] += S.rej;                                                  \
+        counters[2] += S.status != 0;                                          \
     }
+    DFC_DISPATCH_LPC(m.NAP, CALL)
+#undef CALL
     return 0;
 }
 // the mechanism compiler's transport-fit generator (host code, no emulation involved); 0 ok, -2 no transport data
