@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -578,6 +579,69 @@ int dfchem_wdot(dfchem_handle h, int nC, const double* T, const double* p, const
     CUDA_TRY(h, cudaMemcpy2DAsync(dY, nb, Y, (size_t)ldY * sizeof(double), nb, N, cudaMemcpyHostToDevice, s));
     int rc = dfchem_wdot_dev(h, nC, dT, dp, dY, nC, dW, nC, s);
     if (rc != DFCHEM_OK) return rc;
+    CUDA_TRY(h, cudaMemcpy2DAsync(wrate, (size_t)ldW * sizeof(double), dW, nb, nb, N, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(h, cudaStreamSynchronize(s));
+    return DFCHEM_OK;
+}
+
+// ---- dfchem_wdot without any device allocation (no counterpart in the reference; include/dfchem.h) ----------------
+// The scratch of wdot_kernel (work-queue word) and the device staging of the host arrays live in one static device
+// array.  In host code the NAME of that array is only a host-side stand-in: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.  First 256 bytes: queue word; rest: staging.
+constexpr size_t kStaticHead = 256;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticHead + DFCHEM_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mutex;
+unsigned char* g_static_ptr[kStaticMaxDevices] = {};
+
+// device address of g_static_scratch on `device` (which must be current)
+cudaError_t static_scratch_address(int device, unsigned char** out) {
+    if (device < 0 || device >= kStaticMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_ptr[device]) {
+        void* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+        if (e != cudaSuccess) return e;
+        g_static_ptr[device] = static_cast<unsigned char*>(ptr);
+    }
+    *out = g_static_ptr[device];
+    return cudaSuccess;
+}
+}  // namespace
+
+int dfchem_wdot_static(dfchem_handle h, int nC, const double* T, const double* p, const double* Y, int ldY,
+                       double* wrate, int ldW) {
+    if (!h) return DFCHEM_EINVAL;
+    if (nC < 0 || (nC > 0 && (!T || !p || !Y || !wrate)) || ldY < nC || ldW < nC)
+        return fail(h, DFCHEM_EINVAL, "dfchem_wdot_static: bad argument");
+    if (nC == 0) return DFCHEM_OK;
+    const int N = h->mech.N;
+    const size_t per_cell = (2 * (size_t)N + 2) * sizeof(double);
+    if ((size_t)nC * per_cell > (size_t)DFCHEM_STATIC_SCRATCH_BYTES)
+        return fail(h, DFCHEM_EINVAL,
+                    "dfchem_wdot_static: " + std::to_string(nC) + " cells need " + std::to_string((size_t)nC * per_cell) +
+                        " bytes of device staging, the static scratch holds " + std::to_string((size_t)DFCHEM_STATIC_SCRATCH_BYTES) +
+                        " (at most " + std::to_string((size_t)DFCHEM_STATIC_SCRATCH_BYTES / per_cell) +
+                        " cells per call for this mechanism); split the call or use dfchem_wdot");
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    unsigned char* base = nullptr;
+    CUDA_TRY(h, static_scratch_address(h->device, &base));
+    unsigned int* queue = reinterpret_cast<unsigned int*>(base);
+    double* d = reinterpret_cast<double*>(base + kStaticHead);
+    const size_t ld = (size_t)nC, nb = ld * sizeof(double);
+    double *dT = d, *dp = d + ld, *dY = d + 2 * ld, *dW = dY + (size_t)N * ld;
+    cudaStream_t s = h->streams[0];
+    // the array keeps the previous call's contents: the queue word must start at zero
+    CUDA_TRY(h, cudaMemsetAsync(queue, 0, sizeof(unsigned int), s));
+    CUDA_TRY(h, cudaMemcpyAsync(dT, T, nb, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(h, cudaMemcpyAsync(dp, p, nb, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(h, cudaMemcpy2DAsync(dY, nb, Y, (size_t)ldY * sizeof(double), nb, N, cudaMemcpyHostToDevice, s));
+#define CALL(NP, NS) launch_wdot_t<NP, NS>(h, nC, dT, dp, dY, nC, dW, nC, queue, s)
+    DFC_DISPATCH_NP(h->dm.NP, CALL)
+#undef CALL
+    CUDA_TRY(h, cudaGetLastError());
     CUDA_TRY(h, cudaMemcpy2DAsync(wrate, (size_t)ldW * sizeof(double), dW, nb, nb, N, cudaMemcpyDeviceToHost, s));
     CUDA_TRY(h, cudaStreamSynchronize(s));
     return DFCHEM_OK;

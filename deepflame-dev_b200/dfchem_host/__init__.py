@@ -48,6 +48,7 @@ SIGNATURES = {
     "dfchem_tc": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "dfchem_tc_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "dfchem_wdot": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int]),
+    "dfchem_wdot_static": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int]),
     "dfchem_wdot_dev": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]),
     "dfchem_correct_thermo": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
                                       c_void_p, c_void_p, c_void_p, c_int]),
@@ -212,6 +213,13 @@ class Handle:
         nC = T.shape[0]
         out = np.empty((self.N, nC))
         self.check(self.lib.dfchem_wdot(self.h, nC, _ptr(T), _ptr(p), _ptr(Y), Y.shape[1], _ptr(out), nC))
+        return out
+
+    def wdot_static(self, T, p, Y):
+        """dfchem_wdot through the allocation-free entry point (static device scratch, include/dfchem.h)."""
+        nC = T.shape[0]
+        out = np.empty((self.N, nC))
+        self.check(self.lib.dfchem_wdot_static(self.h, nC, _ptr(T), _ptr(p), _ptr(Y), Y.shape[1], _ptr(out), nC))
         return out
 
     def correct_thermo(self, he, p, Y, T, want_cp=False, want_hai=False):

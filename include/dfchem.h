@@ -138,6 +138,20 @@ int dfchem_wdot(dfchem_handle h, int nC, const double* T, const double* p, const
 int dfchem_wdot_dev(dfchem_handle h, int nC, const double* T, const double* p, const double* Y,
                     int ldY, double* wrate, int ldW, void* stream);
 
+/* dfchem_wdot for callers that may not allocate device memory (CUDA graph capture around the call site, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments (host pointers) and same results as dfchem_wdot, but the kernel's scratch -- the
+ * work-queue word and the device staging of T, p, Y and wrate, (2N + 2) doubles per cell -- lives in a file-scope
+ * static device array of DFCHEM_STATIC_SCRATCH_BYTES that every GPU holding the library keeps until exit; the call
+ * makes no cudaMalloc / cudaFree and uses no allocating library routine.  A call whose staging does not fit
+ * returns DFCHEM_EINVAL (dfchem_last_error names the largest nC for this mechanism).  All handles of a process on
+ * one device share the array: calls that overlap on the GPU (two handles, two host threads) race; the call
+ * itself is synchronous, so one caller at a time is safe.  The queue word is zeroed by every call; the staging is
+ * fully overwritten before it is read. */
+#define DFCHEM_STATIC_SCRATCH_BYTES (8u << 20)
+int dfchem_wdot_static(dfchem_handle h, int nC, const double* T, const double* p, const double* Y,
+                       int ldY, double* wrate, int ldW);
+
 /* correctThermo cell loop (dfChemistryModel.C:418-543) without the transport properties:
  * T: in = initial guess, out = solution of h(T, Y/sum Y) = he (Newton, cp slope, |dT|<=100 K
  * per iteration, stop |dT| < 1e-9*T);  psi = Wbar/(R T);  rho = p*psi;  cp [J/kg/K] optional;
