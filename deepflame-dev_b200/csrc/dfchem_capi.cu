@@ -272,13 +272,13 @@ int finish_create(dfchem_ctx* h, int device, dfchem_handle* out) {
     DFC_DISPATCH_NP(h->dm.NP, CALL)
 #undef CALL
     if (e != cudaSuccess) return bail("kernel configuration", e);
-    // Lane-per-cell solve kernel (lane_cell.cuh, gather form).  Measured on B200 (profiles/r2/bench_*_1M_{lane2,warp}.json,
-    // 1,048,576 cells, rtol 1e-6 / atol 1e-10): c7_onestep 1.91e8 vs 1.65e7 cells/s (12x the warp-per-cell kernel), es80
-    // 5.58e6 vs 4.04e6 (1.4x), h2_li 1.29e6 vs 2.45e6 (slower: 8 active species need 2 KB of shared memory per lane, three
-    // warps per SM).  Default: mechanisms with at most 6 active species; DFCHEM_SOLVER=lane / warp forces either kernel.
+    // Lane-per-cell solve kernel (lane_cell.cuh, gather form with ELL lists).  Measured on B200 (profiles/r2/lane_variants.json,
+    // 1,048,576 cells, rtol 1e-6 / atol 1e-10) against the warp-per-cell kernel: c7_onestep 2.69e8 vs 1.65e7 cells/s (16x), es80
+    // 1.2e7 vs 4.0e6 (3x), h2_li 5.5e6 vs 2.5e6 (2.2x).  Default: mechanisms with at most 8 active species (padded sizes 4 / 6 / 8;
+    // the 12-wide instantiation spills and stays opt-in); DFCHEM_SOLVER=lane / warp forces either kernel.
     const char* solver_env = std::getenv("DFCHEM_SOLVER");
     const std::string solver = solver_env ? solver_env : "";
-    constexpr int kLpcAutoActive = 6;
+    constexpr int kLpcAutoActive = 8;
     if (solver == "lane" || (solver != "warp" && h->dm.NA <= kLpcAutoActive)) {
         h->lpc = build_lpc_tables(h->mech, h->ht.perm, h->dm.NA);
         if (h->lpc.usable) {

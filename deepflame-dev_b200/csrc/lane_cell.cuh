@@ -25,6 +25,12 @@ constexpr int kLS = 1;
 constexpr int kLpcLanes = 32;
 
 #define LPC_AT(off, i) L[((off) + (i)) * kLS]
+#ifndef LPC_PAIR
+#define LPC_PAIR 0   // reaction loop by pairs: measured +2 % on es80, -18 % on h2_li, -6 % on c7_onestep (profiles/r2): off
+#endif
+#ifndef LPC_ROLLED
+#define LPC_ROLLED 1  // the six RODAS stages as a real loop (a third less code)
+#endif
 
 struct LpcState {  // per-lane integrator state (registers)
     double t, h, dt, rho_ct, ysum, h_free;
@@ -35,7 +41,8 @@ struct LpcState {  // per-lane integrator state (registers)
 // compile-time offsets (doubles per lane) of the fixed region
 template <int NAP>
 struct LpcFixed {
-    static constexpr int J = 0, LU = NAP * NAP, K = 2 * NAP * NAP, F0 = K + 6 * NAP, DC = F0 + NAP;
+    static constexpr int J = 0, LU = NAP * NAP, K = (lpc_lu_in_regs(NAP) ? 1 : 2) * NAP * NAP, F0 = K + 6 * NAP, DC = F0 + NAP;
+    static_assert(DC + NAP == lpc_fixed_doubles(NAP), "fixed region");
 };
 
 // LpcMech whose tables point into a copy of the blob at `nb` (shared memory)
@@ -47,11 +54,10 @@ DFC_HD LpcMech lpc_rebase(const LpcMech& m, const uint8_t* nb) {
     LPC_REBASE(eff, double);
     LPC_REBASE(fall, double);
     LPC_REBASE(arrh, double);
-    LPC_REBASE(fptr, int);
-    LPC_REBASE(fidx, int);
+    LPC_REBASE(fidx, uint32_t);
     LPC_REBASE(fcoef, double);
-    LPC_REBASE(jptr, int);
-    LPC_REBASE(jidx, int);
+    LPC_REBASE(jrow, int);
+    LPC_REBASE(jidx, uint32_t);
     LPC_REBASE(jcoef, double);
     LPC_REBASE(gptr, int);
     LPC_REBASE(gidx, int);
@@ -86,6 +92,7 @@ DFC_HD void lpc_load_state(const LpcMech& m, double* L, const double* Y, int ldY
     }
     LPC_AT(m.off_c, m.N) = 1.0;   // the "absent factor" slot
     LPC_AT(m.off_cs, m.N) = 1.0;
+    LPC_AT(m.off_q, m.q_zero) = 0.0;   // the padding slot of the wdot lists
     DFC_UNROLL
     for (int i = 0; i < NAP; ++i) LPC_AT(LpcFixed<NAP>::DC, i) = 0.0;
     S.ysum = s;
@@ -133,99 +140,158 @@ DFC_HD void lpc_setup(const LpcMech& m, double* L, double T) {
     }
 }
 
-// Reaction loop: q_r -> column off_q (and, if JAC, the partial derivatives -> column off_dq).  Stores only.
+// Rate of progress of reaction r at the concentrations in column off_cx, all in registers: q, the forward and
+// reverse parts, and (if JAC) the partial derivatives in slot order (present reactant factors, present product
+// factors, d q/d[M]); `mask` bit a = derivative a is present.  Loads only: two calls in a row have no store
+// between their loads, so the compiler can overlap the load -> multiply chains of two reactions.
+struct LpcRate {
+    double q, qf, qr, d[7];
+    uint32_t mask;
+};
+template <bool JAC>
+DFC_HD void lpc_rate(const LpcMech& m, const double* L, int off_cx, int r, const LpcRx& x, LpcRate& o) {
+    const uint32_t none = (uint32_t)m.N;
+    const uint32_t kind = x.x & 3u;
+    const uint32_t fo[3] = {(x.x >> 8) & 63u, (x.x >> 14) & 63u, (x.x >> 20) & 63u};
+    const uint32_t po[3] = {x.y & 63u, (x.y >> 6) & 63u, (x.y >> 12) & 63u};
+    double fv[3], fd[3], pv[3], pd[3];
+    if (!(x.x & 8u)) {
+        DFC_UNROLL
+        for (int a = 0; a < 3; ++a) {
+            fv[a] = LPC_AT(off_cx, fo[a]);
+            pv[a] = LPC_AT(off_cx, po[a]);
+            fd[a] = 1.0;
+            pd[a] = 1.0;
+        }
+    } else {  // fractional / large orders: c^o with Cantera's rule (non-positive c -> 0)
+        const double* pw = m.powtab + (size_t)((x.z >> 8) & 0xFFu) * 9;
+        for (int a = 0; a < 3; ++a) {
+            fv[a] = pv[a] = 1.0;
+            fd[a] = pd[a] = 0.0;
+            if (fo[a] != none) {
+                const D2 t = pow_factor(pw[a], LPC_AT(off_cx, fo[a]));
+                fv[a] = t.x;
+                fd[a] = t.y;
+            }
+            if (po[a] != none) {
+                const D2 t = pow_factor(pw[6 + a], LPC_AT(off_cx, po[a]));
+                pv[a] = t.x;
+                pd[a] = t.y;
+            }
+        }
+    }
+    double kfe = LPC_AT(m.off_kf, r);
+    const double rkc = LPC_AT(m.off_rkc, r);
+    double dkdM = 0.0;
+    if (kind != (uint32_t)kElementary) {
+        const double* ef = m.eff + (size_t)(x.y >> 20) * m.N;
+        double M0 = 0.0, M1 = 0.0;
+        int k = 0;
+        for (; k + 1 < m.N; k += 2) {
+            M0 = fma(ef[k], LPC_AT(off_cx, k), M0);
+            M1 = fma(ef[k + 1], LPC_AT(off_cx, k + 1), M1);
+        }
+        if (k < m.N) M0 = fma(ef[k], LPC_AT(off_cx, k), M0);
+        const double M = M0 + M1;
+        if (kind == (uint32_t)kThreeBody) {
+            dkdM = kfe;
+            kfe *= M;
+        } else {
+            const int fid = (int)(x.z & 0xFFu);
+            const double rk = LPC_AT(m.off_k0, fid);  // k0 / kinf
+            const double pr = M * rk;
+            double F = 1.0, dF_dpr = 0.0;
+            if (kind == (uint32_t)kFalloffTroe) {
+                const double lf = LPC_AT(m.off_lfc, fid);
+                const double lpr = log10(fmax(pr, kSmall));
+                const double cc = -0.4 - 0.67 * lf;
+                const double nn = 0.75 - 1.27 * lf;
+                const double xx = lpr + cc;
+                const double rden = 1.0 / (nn - 0.14 * xx);
+                const double f1 = xx * rden;
+                const double g = 1.0 / (1.0 + f1 * f1);
+                F = exp10(lf * g);
+                if (JAC && pr > kSmall) dF_dpr = F * (-lf * 2.0 * f1 * g * g * (nn * rden * rden)) / pr;
+            }
+            const double ip = 1.0 / (1.0 + pr);
+            if (JAC) dkdM = kfe * (F * ip * ip + pr * ip * dF_dpr) * rk;
+            kfe = kfe * (pr * ip) * F;
+        }
+    }
+    const double Pf = fv[0] * fv[1] * fv[2];
+    const double Pp = pv[0] * pv[1] * pv[2];
+    const double kre = kfe * rkc;
+    o.qf = kfe * Pf;
+    o.qr = kre * Pp;
+    o.q = kfe * Pf - kre * Pp;
+    if (JAC) {
+        o.mask = (fo[0] != none ? 1u : 0u) | (fo[1] != none ? 2u : 0u) | (fo[2] != none ? 4u : 0u) | (po[0] != none ? 8u : 0u) |
+                 (po[1] != none ? 16u : 0u) | (po[2] != none ? 32u : 0u) | (kind != (uint32_t)kElementary ? 64u : 0u);
+        o.d[0] = kfe * fd[0] * fv[1] * fv[2];
+        o.d[1] = kfe * fv[0] * fd[1] * fv[2];
+        o.d[2] = kfe * fv[0] * fv[1] * fd[2];
+        o.d[3] = -kre * pd[0] * pv[1] * pv[2];
+        o.d[4] = -kre * pv[0] * pd[1] * pv[2];
+        o.d[5] = -kre * pv[0] * pv[1] * pd[2];
+        o.d[6] = dkdM * (Pf - rkc * Pp);
+    }
+}
+template <bool JAC>
+DFC_HD void lpc_rate_store(const LpcMech& m, double* L, int r, const LpcRx& x, const LpcRate& o, double* qf_out, double* qr_out,
+                           size_t ldq) {
+    LPC_AT(m.off_q, r) = o.q;
+    if (qf_out) {
+        const size_t p = (size_t)(x.z >> 16) * ldq;
+        qf_out[p] = o.qf;
+        qr_out[p] = o.qr;
+    }
+    if (JAC) {
+        int slot = m.off_dq + (int)x.w;
+        DFC_UNROLL
+        for (int a = 0; a < 7; ++a)
+            if (o.mask & (1u << a)) LPC_AT(slot++, 0) = o.d[a];
+    }
+}
+
+// Reaction loop: q_r -> column off_q (and, if JAC, the partial derivatives -> column off_dq), two reactions per
+// iteration (all loads of both before the first store).
 template <bool JAC>
 DFC_HD void lpc_reactions(const LpcMech& m, double* L, int off_cx, double* qf_out = nullptr, double* qr_out = nullptr,
                           size_t ldq = 0) {
-    const uint32_t none = (uint32_t)m.N;
+    int r = 0;
+#if LPC_PAIR
     DFC_NOUNROLL
-    for (int r = 0; r < m.R; ++r) {
+    for (; r + 1 < m.R; r += 2) {
+        const LpcRx x0 = m.rx[r], x1 = m.rx[r + 1];
+        LpcRate o0, o1;
+        lpc_rate<JAC>(m, L, off_cx, r, x0, o0);
+        lpc_rate<JAC>(m, L, off_cx, r + 1, x1, o1);
+        lpc_rate_store<JAC>(m, L, r, x0, o0, qf_out, qr_out, ldq);
+        lpc_rate_store<JAC>(m, L, r + 1, x1, o1, qf_out, qr_out, ldq);
+    }
+#endif
+    DFC_NOUNROLL
+    for (; r < m.R; ++r) {
         const LpcRx x = m.rx[r];
-        const uint32_t kind = x.x & 3u;
-        const uint32_t fo[3] = {(x.x >> 8) & 63u, (x.x >> 14) & 63u, (x.x >> 20) & 63u};
-        const uint32_t po[3] = {x.y & 63u, (x.y >> 6) & 63u, (x.y >> 12) & 63u};
-        double fv[3], fd[3], pv[3], pd[3];
-        if (!(x.x & 8u)) {
-            DFC_UNROLL
-            for (int a = 0; a < 3; ++a) {
-                fv[a] = LPC_AT(off_cx, fo[a]);
-                pv[a] = LPC_AT(off_cx, po[a]);
-                fd[a] = 1.0;
-                pd[a] = 1.0;
-            }
-        } else {  // fractional / large orders: c^o with Cantera's rule (non-positive c -> 0)
-            const double* pw = m.powtab + (size_t)((x.z >> 8) & 0xFFu) * 9;
-            for (int a = 0; a < 3; ++a) {
-                fv[a] = pv[a] = 1.0;
-                fd[a] = pd[a] = 0.0;
-                if (fo[a] != none) {
-                    const D2 t = pow_factor(pw[a], LPC_AT(off_cx, fo[a]));
-                    fv[a] = t.x;
-                    fd[a] = t.y;
-                }
-                if (po[a] != none) {
-                    const D2 t = pow_factor(pw[6 + a], LPC_AT(off_cx, po[a]));
-                    pv[a] = t.x;
-                    pd[a] = t.y;
-                }
-            }
-        }
-        double kfe = LPC_AT(m.off_kf, r);
-        const double rkc = LPC_AT(m.off_rkc, r);
-        double dkdM = 0.0;
-        if (kind != (uint32_t)kElementary) {
-            const double* ef = m.eff + (size_t)(x.y >> 20) * m.N;
-            double M0 = 0.0, M1 = 0.0;
-            int k = 0;
-            for (; k + 1 < m.N; k += 2) {
-                M0 = fma(ef[k], LPC_AT(off_cx, k), M0);
-                M1 = fma(ef[k + 1], LPC_AT(off_cx, k + 1), M1);
-            }
-            if (k < m.N) M0 = fma(ef[k], LPC_AT(off_cx, k), M0);
-            const double M = M0 + M1;
-            if (kind == (uint32_t)kThreeBody) {
-                dkdM = kfe;
-                kfe *= M;
-            } else {
-                const int fid = (int)(x.z & 0xFFu);
-                const double rk = LPC_AT(m.off_k0, fid);  // k0 / kinf
-                const double pr = M * rk;
-                double F = 1.0, dF_dpr = 0.0;
-                if (kind == (uint32_t)kFalloffTroe) {
-                    const double lf = LPC_AT(m.off_lfc, fid);
-                    const double lpr = log10(fmax(pr, kSmall));
-                    const double cc = -0.4 - 0.67 * lf;
-                    const double nn = 0.75 - 1.27 * lf;
-                    const double xx = lpr + cc;
-                    const double rden = 1.0 / (nn - 0.14 * xx);
-                    const double f1 = xx * rden;
-                    const double g = 1.0 / (1.0 + f1 * f1);
-                    F = exp10(lf * g);
-                    if (JAC && pr > kSmall) dF_dpr = F * (-lf * 2.0 * f1 * g * g * (nn * rden * rden)) / pr;
-                }
-                const double ip = 1.0 / (1.0 + pr);
-                if (JAC) dkdM = kfe * (F * ip * ip + pr * ip * dF_dpr) * rk;
-                kfe = kfe * (pr * ip) * F;
-            }
-        }
-        const double Pf = fv[0] * fv[1] * fv[2];
-        const double Pp = pv[0] * pv[1] * pv[2];
-        const double kre = kfe * rkc;
-        LPC_AT(m.off_q, r) = kfe * Pf - kre * Pp;
-        if (qf_out) {
-            const size_t o = (size_t)(x.z >> 16) * ldq;
-            qf_out[o] = kfe * Pf;
-            qr_out[o] = kre * Pp;
-        }
-        if (JAC) {
-            int slot = m.off_dq + (int)x.w;
-            if (fo[0] != none) LPC_AT(slot++, 0) = kfe * fd[0] * fv[1] * fv[2];
-            if (fo[1] != none) LPC_AT(slot++, 0) = kfe * fv[0] * fd[1] * fv[2];
-            if (fo[2] != none) LPC_AT(slot++, 0) = kfe * fv[0] * fv[1] * fd[2];
-            if (po[0] != none) LPC_AT(slot++, 0) = -kre * pd[0] * pv[1] * pv[2];
-            if (po[1] != none) LPC_AT(slot++, 0) = -kre * pv[0] * pd[1] * pv[2];
-            if (po[2] != none) LPC_AT(slot++, 0) = -kre * pv[0] * pv[1] * pd[2];
-            if (kind != (uint32_t)kElementary) LPC_AT(slot, 0) = dkdM * (Pf - rkc * Pp);
+        LpcRate o;
+        lpc_rate<JAC>(m, L, off_cx, r, x, o);
+        lpc_rate_store<JAC>(m, L, r, x, o, qf_out, qr_out, ldq);
+    }
+}
+
+// acc[t] = sum_k coef[k][t] * column[idx[k][t]]: one ELL row (lpc_tables.hpp) feeds all NAP targets, i.e. NAP
+// independent load -> multiply-add chains per iteration, accumulators in registers
+template <int NAP>
+DFC_HD void lpc_gather(const uint32_t* idx, const double* coef, int rows, const double* L, int off_col, double (&acc)[NAP]) {
+    DFC_UNROLL
+    for (int t = 0; t < NAP; ++t) acc[t] = 0.0;
+    for (int k = 0; k < rows; ++k, idx += NAP / 2, coef += NAP) {
+        DFC_UNROLL
+        for (int w = 0; w < NAP / 2; ++w) {
+            const uint32_t u = idx[w];
+            const D2 c = ld2(coef + 2 * w);
+            acc[2 * w] = fma(c.x, LPC_AT(off_col, u & 0xFFFFu), acc[2 * w]);
+            acc[2 * w + 1] = fma(c.y, LPC_AT(off_col, u >> 16), acc[2 * w + 1]);
         }
     }
 }
@@ -234,39 +300,28 @@ DFC_HD void lpc_reactions(const LpcMech& m, double* L, int off_cx, double* qf_ou
 template <int NAP, bool JAC>
 DFC_HD void lpc_eval(const LpcMech& m, double* L, int off_cx, double (&f)[NAP]) {
     lpc_reactions<JAC>(m, L, off_cx);
-    DFC_UNROLL
-    for (int i = 0; i < NAP; ++i) {
-        double a0 = 0.0, a1 = 0.0;
-        int e = m.fptr[i];
-        const int e1 = m.fptr[i + 1];
-        for (; e + 1 < e1; e += 2) {
-            a0 = fma(m.fcoef[e], LPC_AT(m.off_q, m.fidx[e]), a0);
-            a1 = fma(m.fcoef[e + 1], LPC_AT(m.off_q, m.fidx[e + 1]), a1);
-        }
-        if (e < e1) a0 = fma(m.fcoef[e], LPC_AT(m.off_q, m.fidx[e]), a0);
-        f[i] = a0 + a1;
-    }
+    lpc_gather<NAP>(m.fidx, m.fcoef, m.f_rows, L, m.off_q, f);
     if (JAC) {
-        DFC_UNROLL
-        for (int ij = 0; ij < NAP * NAP; ++ij) {
-            double a0 = 0.0, a1 = 0.0;
-            int e = m.jptr[ij];
-            const int e1 = m.jptr[ij + 1];
-            for (; e + 1 < e1; e += 2) {
-                a0 = fma(m.jcoef[e], LPC_AT(m.off_dq, m.jidx[e]), a0);
-                a1 = fma(m.jcoef[e + 1], LPC_AT(m.off_dq, m.jidx[e + 1]), a1);
-            }
-            if (e < e1) a0 = fma(m.jcoef[e], LPC_AT(m.off_dq, m.jidx[e]), a0);
-            LPC_AT(LpcFixed<NAP>::J, ij) = a0 + a1;
+        LPC_AT(m.off_dq, m.n_dq) = 0.0;  // the padding slot of the lists (the column aliases the LU / stage region)
+        DFC_NOUNROLL
+        for (int i = 0; i < NAP; ++i) {
+            const int k0 = m.jrow[i];
+            double a[NAP];
+            lpc_gather<NAP>(m.jidx + (size_t)k0 * (NAP / 2), m.jcoef + (size_t)k0 * NAP, m.jrow[i + 1] - k0, L, m.off_dq, a);
+            DFC_UNROLL
+            for (int j = 0; j < NAP; ++j) LPC_AT(LpcFixed<NAP>::J, i * NAP + j) = a[j];
         }
     }
 }
 
-// A = I/(h g) - J, LU in registers without pivoting (1/pivot stored on the diagonal), factors -> fixed region.
-// Returns the number of negative pivots (unstable-mode guard, integrator.cuh).
+// A = I/(h g) - J, LU in registers without pivoting (1/pivot stored on the diagonal).  The factors stay in the
+// caller's registers for the six stage solves when the matrix is small (lpc_lu_in_regs), else they go to the
+// fixed region.  Returns the number of negative pivots (unstable-mode guard, integrator.cuh).
 template <int NAP>
-DFC_HD int lpc_factor_matrix(double* L, double inv_hg) {
-    double A[NAP][NAP];
+constexpr bool lpc_lu_in_regs() { return lpc_lu_in_regs(NAP); }
+
+template <int NAP>
+DFC_HD int lpc_factor_matrix(double* L, double inv_hg, double (&A)[NAP][NAP]) {
     DFC_UNROLL
     for (int i = 0; i < NAP; ++i) {
         DFC_UNROLL
@@ -286,27 +341,31 @@ DFC_HD int lpc_factor_matrix(double* L, double inv_hg) {
             for (int j = k + 1; j < NAP; ++j) A[i][j] = fma(-l, A[k][j], A[i][j]);
         }
     }
-    DFC_UNROLL
-    for (int i = 0; i < NAP; ++i) {
+    if (!lpc_lu_in_regs<NAP>()) {
         DFC_UNROLL
-        for (int j = 0; j < NAP; ++j) LPC_AT(LpcFixed<NAP>::LU, i * NAP + j) = A[i][j];
+        for (int i = 0; i < NAP; ++i) {
+            DFC_UNROLL
+            for (int j = 0; j < NAP; ++j) LPC_AT(LpcFixed<NAP>::LU, i * NAP + j) = A[i][j];
+        }
     }
     return neg;
 }
-// x <- A^-1 x, x in registers, factors read at compile-time offsets
+// x <- A^-1 x, x in registers; factors from registers or from the fixed region (compile-time offsets)
 template <int NAP>
-DFC_HD void lpc_lu_solve(const double* L, double (&x)[NAP]) {
+DFC_HD void lpc_lu_solve(const double* L, const double (&A)[NAP][NAP], double (&x)[NAP]) {
+#define LPC_LU(i, j) (lpc_lu_in_regs<NAP>() ? A[i][j] : LPC_AT(LpcFixed<NAP>::LU, (i) * NAP + (j)))
     DFC_UNROLL
     for (int i = 1; i < NAP; ++i) {
         DFC_UNROLL
-        for (int j = 0; j < i; ++j) x[i] = fma(-LPC_AT(LpcFixed<NAP>::LU, i * NAP + j), x[j], x[i]);
+        for (int j = 0; j < i; ++j) x[i] = fma(-LPC_LU(i, j), x[j], x[i]);
     }
     DFC_UNROLL
     for (int i = NAP - 1; i >= 0; --i) {
         DFC_UNROLL
-        for (int j = i + 1; j < NAP; ++j) x[i] = fma(-LPC_AT(LpcFixed<NAP>::LU, i * NAP + j), x[j], x[i]);
-        x[i] *= LPC_AT(LpcFixed<NAP>::LU, i * NAP + i);
+        for (int j = i + 1; j < NAP; ++j) x[i] = fma(-LPC_LU(i, j), x[j], x[i]);
+        x[i] *= LPC_LU(i, i);
     }
+#undef LPC_LU
 }
 
 template <int NAP>
@@ -330,9 +389,43 @@ DFC_HD void lpc_begin_cell(const LpcMech& m, double* L, const SolveArgs& a, int 
     }
 }
 
-// stage I of RODAS4 with I a compile-time constant: stage point, rate evaluation, right-hand side, solve
+// stage i of RODAS4: stage point, rate evaluation, right-hand side, solve.  LPC_ROLLED: i is a run-time value and
+// the six stages are one loop body (the coefficient of a (stage, j) pair is looked up once and applied to all
+// rows; same operation order per row as the unrolled form, so the results are identical).
+#if LPC_ROLLED
+template <int NAP>
+DFC_HD void lpc_stage(const LpcMech& m, double* L, const double (&A)[NAP][NAP], double ih, int i) {
+    using F = LpcFixed<NAP>;
+    double x[NAP];
+    if (i == 0) {
+        DFC_UNROLL
+        for (int row = 0; row < NAP; ++row) x[row] = LPC_AT(F::F0, row);
+    } else {
+        double v[NAP];
+        DFC_UNROLL
+        for (int row = 0; row < NAP; ++row) v[row] = LPC_AT(m.off_c, row);
+        for (int j = 0; j < i; ++j) {
+            const double aj = rodas_a(i, j);
+            DFC_UNROLL
+            for (int row = 0; row < NAP; ++row) v[row] = fma(aj, LPC_AT(F::K, j * NAP + row), v[row]);
+        }
+        DFC_UNROLL
+        for (int row = 0; row < NAP; ++row)
+            if (row < m.NA) LPC_AT(m.off_cs, row) = v[row];
+        lpc_eval<NAP, false>(m, L, m.off_cs, x);
+        for (int j = 0; j < i; ++j) {
+            const double cj = rodas_c(i, j) * ih;
+            DFC_UNROLL
+            for (int row = 0; row < NAP; ++row) x[row] = fma(cj, LPC_AT(F::K, j * NAP + row), x[row]);
+        }
+    }
+    lpc_lu_solve<NAP>(L, A, x);
+    DFC_UNROLL
+    for (int row = 0; row < NAP; ++row) LPC_AT(F::K, i * NAP + row) = x[row];
+}
+#else
 template <int NAP, int I>
-DFC_HD void lpc_stage(const LpcMech& m, double* L, double ih) {
+DFC_HD void lpc_stage(const LpcMech& m, double* L, const double (&A)[NAP][NAP], double ih) {
     using F = LpcFixed<NAP>;
     double x[NAP];
     if (I == 0) {
@@ -354,10 +447,11 @@ DFC_HD void lpc_stage(const LpcMech& m, double* L, double ih) {
             for (int j = 0; j < I; ++j) x[row] = fma(rodas_c(I, j) * ih, LPC_AT(F::K, j * NAP + row), x[row]);
         }
     }
-    lpc_lu_solve<NAP>(L, x);
+    lpc_lu_solve<NAP>(L, A, x);
     DFC_UNROLL
     for (int row = 0; row < NAP; ++row) LPC_AT(F::K, I * NAP + row) = x[row];
 }
+#endif
 
 // One step attempt of the cell on this lane (the body of integrate_cell's loops).  Returns true
 // when the sub-step is complete (or has failed: S.status).
@@ -397,18 +491,24 @@ DFC_HD bool lpc_attempt(const LpcMech& m, double* L, LpcState& S, double rtol, d
     }
     const bool cut = hs < S.h;
     const double ih = 1.0 / hs;
-    if (lpc_factor_matrix<NAP>(L, ih / kGamma) & 1) {  // unstable-mode guard
+    double A[NAP][NAP];
+    if (lpc_factor_matrix<NAP>(L, ih / kGamma, A) & 1) {  // unstable-mode guard
         ++S.rej;
         S.after_reject = true;
         S.h = hs * kFacUnstable;
         return false;
     }
-    lpc_stage<NAP, 0>(m, L, ih);
-    lpc_stage<NAP, 1>(m, L, ih);
-    lpc_stage<NAP, 2>(m, L, ih);
-    lpc_stage<NAP, 3>(m, L, ih);
-    lpc_stage<NAP, 4>(m, L, ih);
-    lpc_stage<NAP, 5>(m, L, ih);
+#if LPC_ROLLED
+    DFC_NOUNROLL
+    for (int i = 0; i < kStages; ++i) lpc_stage<NAP>(m, L, A, ih, i);
+#else
+    lpc_stage<NAP, 0>(m, L, A, ih);
+    lpc_stage<NAP, 1>(m, L, A, ih);
+    lpc_stage<NAP, 2>(m, L, A, ih);
+    lpc_stage<NAP, 3>(m, L, A, ih);
+    lpc_stage<NAP, 4>(m, L, A, ih);
+    lpc_stage<NAP, 5>(m, L, A, ih);
+#endif
     // new solution = argument of the last stage + k_6; error estimate = k_6
     double inc[NAP];
     double e2 = 0.0;

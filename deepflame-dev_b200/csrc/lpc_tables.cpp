@@ -31,10 +31,9 @@ LpcMech HostLpc::rebase(const void* base) const {
     d.eff = shift(d.eff, base);
     d.fall = shift(d.fall, base);
     d.arrh = shift(d.arrh, base);
-    d.fptr = shift(d.fptr, base);
     d.fidx = shift(d.fidx, base);
     d.fcoef = shift(d.fcoef, base);
-    d.jptr = shift(d.jptr, base);
+    d.jrow = shift(d.jrow, base);
     d.jidx = shift(d.jidx, base);
     d.jcoef = shift(d.jcoef, base);
     d.gptr = shift(d.gptr, base);
@@ -178,16 +177,31 @@ HostLpc build_lpc_tables(const Mechanism& m, const std::vector<int>& perm, int N
     if (n_dq > 0xFFFF) return h;
     std::vector<double> eff;
     for (auto& s : sets) eff.insert(eff.end(), s.begin(), s.end());
-    std::vector<int> fptr{0}, fidx, jptr{0}, jidx;
+    // ELL form of the gather lists (lpc_tables.hpp): `rows` x NAP entries, padded with (zero slot, 0.0)
+    const int q_zero = std::max(R, N);
+    auto ell = [&](const std::vector<std::pair<int, double>>* lists, int zero, std::vector<uint32_t>& idx,
+                   std::vector<double>& coef) {
+        size_t rows = 0;
+        for (int t = 0; t < NAP; ++t) rows = std::max(rows, lists[t].size());
+        for (size_t k = 0; k < rows; ++k) {
+            for (int t = 0; t < NAP; t += 2) {
+                uint32_t w = 0;
+                for (int u = 0; u < 2; ++u) {
+                    const bool has = k < lists[t + u].size();
+                    w |= (uint32_t)(has ? lists[t + u][k].first : zero) << (16 * u);
+                    coef.push_back(has ? lists[t + u][k].second : 0.0);
+                }
+                idx.push_back(w);
+            }
+        }
+        return (int)rows;
+    };
+    std::vector<uint32_t> fidx, jidx;
     std::vector<double> fcoef, jcoef;
-    for (auto& l : flist) {
-        for (auto& e : l) fidx.push_back(e.first), fcoef.push_back(e.second);
-        fptr.push_back((int)fidx.size());
-    }
-    for (auto& l : jlist) {
-        for (auto& e : l) jidx.push_back(e.first), jcoef.push_back(e.second);
-        jptr.push_back((int)jidx.size());
-    }
+    std::vector<int> jrow{0};
+    if (q_zero > 0xFFFF) return h;
+    const int f_rows = ell(flist.data(), q_zero, fidx, fcoef);
+    for (int i = 0; i < NAP; ++i) jrow.push_back(jrow.back() + ell(jlist.data() + (size_t)i * NAP, n_dq, jidx, jcoef));
     std::vector<double> W(N), Tmid(N), nasa((size_t)N * 14), hc(N);
     for (int i = 0; i < N; ++i) {
         const int k = perm[i];
@@ -212,20 +226,20 @@ HostLpc build_lpc_tables(const Mechanism& m, const std::vector<int>& perm, int N
     L.off_rkc = take(R);
     L.off_k0 = take(n_fall);
     L.off_lfc = take(n_fall);
-    L.off_q = take(std::max(R, N));   // doubles as the g/RT scratch of the set-up
-    const int alias_room = NAP * NAP + 6 * NAP;   // LU + stage vectors
-    L.off_dq = n_dq <= alias_room ? NAP * NAP : take(n_dq);
+    L.off_q = take(std::max(R, N) + 1);   // doubles as the g/RT scratch of the set-up; last slot: 0.0 (list padding)
+    L.f_rows = f_rows;
+    L.q_zero = q_zero;
+    L.off_dq = n_dq + 1 <= lpc_alias_room(NAP) ? NAP * NAP : take(n_dq + 1);   // slot n_dq: 0.0 (list padding)
     L.lane_doubles = off;
     L.rx = reinterpret_cast<const LpcRx*>(blob_add(h.blob, rx));
     L.powtab = reinterpret_cast<const double*>(blob_add(h.blob, powtab));
     L.eff = reinterpret_cast<const double*>(blob_add(h.blob, eff));
     L.fall = reinterpret_cast<const double*>(blob_add(h.blob, fall));
     L.arrh = reinterpret_cast<const double*>(blob_add(h.blob, arrh));
-    L.fptr = reinterpret_cast<const int*>(blob_add(h.blob, fptr));
-    L.fidx = reinterpret_cast<const int*>(blob_add(h.blob, fidx));
+    L.fidx = reinterpret_cast<const uint32_t*>(blob_add(h.blob, fidx));
     L.fcoef = reinterpret_cast<const double*>(blob_add(h.blob, fcoef));
-    L.jptr = reinterpret_cast<const int*>(blob_add(h.blob, jptr));
-    L.jidx = reinterpret_cast<const int*>(blob_add(h.blob, jidx));
+    L.jrow = reinterpret_cast<const int*>(blob_add(h.blob, jrow));
+    L.jidx = reinterpret_cast<const uint32_t*>(blob_add(h.blob, jidx));
     L.jcoef = reinterpret_cast<const double*>(blob_add(h.blob, jcoef));
     L.gptr = reinterpret_cast<const int*>(blob_add(h.blob, gptr));
     L.gidx = reinterpret_cast<const int*>(blob_add(h.blob, gidx));

@@ -9,7 +9,9 @@
 // derivatives d q_r / d c_j go to per-lane shared-memory columns); wdot_i and J_ij are then summed
 // from per-target entry lists in loops whose TARGET index is a compile-time constant (the kernel is
 // templated on the padded species count), so the accumulators live in registers and no shared-memory
-// read-modify-write chain exists anywhere.
+// read-modify-write chain exists anywhere.  The lists are stored in ELL form (third version): one row
+// serves all NAP targets at once, which gives the lane NAP independent load -> multiply-add chains
+// per iteration instead of one list walked after the other.
 #pragma once
 #include <cstdint>
 #include <vector>
@@ -48,11 +50,15 @@ struct LpcMech {
     const double* eff;         // [n_msets * N] dense efficiencies, internal order
     const double* fall;        // [n_fall * 8] ln A0, b0, Ta0, Troe A, T3, T1, T2, is_troe
     const double* arrh;        // [R * 3] ln A, b, Ta
-    const int* fptr;           // [NAP + 1] wdot gather lists: entries fidx (reaction), fcoef (nu)
-    const int* fidx;
-    const double* fcoef;
-    const int* jptr;           // [NAP*NAP + 1] Jacobian gather lists: entries jidx (dq slot), jcoef
-    const int* jidx;
+    // gather lists in ELL form: row k of a list set holds ONE entry for each of the NAP targets (padded with
+    // coefficient 0 and the index of a slot that always holds 0.0), so a gather is `rows` iterations of NAP
+    // independent multiply-adds.  Indices are 16-bit, two per word: target t -> word t/2, half t%2.
+    int f_rows;                // wdot: targets = species, entries (reaction, nu); zero slot = q[q_zero]
+    int q_zero;
+    const uint32_t* fidx;      // [f_rows][NAP/2]
+    const double* fcoef;       // [f_rows][NAP]
+    const int* jrow;           // [NAP + 1] Jacobian: matrix row i uses ELL rows jrow[i] .. jrow[i+1], targets = columns,
+    const uint32_t* jidx;      //   entries (dq slot, coefficient); zero slot = dq[n_dq]
     const double* jcoef;
     const int* gptr;           // [R + 1] equilibrium-constant lists: entries gidx (species), gcoef (net nu)
     const int* gidx;
@@ -72,8 +78,14 @@ struct HostLpc {
 };
 
 constexpr int lpc_pad(int NA) { return NA <= 4 ? 4 : NA <= 6 ? 6 : NA <= 8 ? 8 : 12; }
-// per-lane doubles of the fixed region: J, LU, six stage vectors, f0, dc
-constexpr int lpc_fixed_doubles(int NAP) { return 2 * NAP * NAP + 8 * NAP; }
+// up to 6 x 6 the LU factors of a step attempt stay in the lane's registers for the six stage solves (72 registers);
+// larger matrices keep them in the fixed region
+constexpr bool lpc_lu_in_regs(int NAP) { return NAP <= 6; }
+// per-lane doubles of the fixed region: J, [LU,] six stage vectors, f0, dc
+constexpr int lpc_fixed_doubles(int NAP) { return (lpc_lu_in_regs(NAP) ? 1 : 2) * NAP * NAP + 8 * NAP; }
+// room for the derivative column where it aliases dead arrays of the fixed region, starting at offset NAP*NAP: the
+// stage vectors and f0 (LU in registers) or the LU factors and the stage vectors
+constexpr int lpc_alias_room(int NAP) { return lpc_lu_in_regs(NAP) ? 7 * NAP : NAP * NAP + 6 * NAP; }
 
 // perm: internal -> caller species index with the NA active species first (HostTables::perm)
 HostLpc build_lpc_tables(const Mechanism& m, const std::vector<int>& perm, int NA);

@@ -189,6 +189,14 @@ int emu_solve_lpc(void* h, int nC, const double* T, const double* p, const doubl
 #undef CALL
     return 0;
 }
+// layout of the lane-per-cell tables: {usable, NAP, lane_doubles, n_dq, f_rows, Jacobian ELL rows, table bytes, off_dq}
+void emu_lpc_info(void* h, int* out) {
+    const Emu* e = static_cast<Emu*>(h);
+    HostLpc lpc = build_lpc_tables(e->mech, e->ht.perm, e->dm.NA);
+    const LpcMech m = lpc.usable ? lpc.rebase(lpc.blob.data()) : LpcMech{};
+    const int v[8] = {lpc.usable ? 1 : 0, m.NAP, m.lane_doubles, m.n_dq, m.f_rows, lpc.usable ? m.jrow[m.NAP] : 0, m.bytes, m.off_dq};
+    std::memcpy(out, v, sizeof(v));
+}
 // the mechanism compiler's transport-fit generator (host code, no emulation involved); 0 ok, -2 no transport data
 int emu_transport_fits(void* h, double* visc, double* cond, double* diff) {
     const Emu* e = static_cast<Emu*>(h);
