@@ -207,6 +207,8 @@ def main():
     ap.add_argument("--no-configs", action="store_true", help="skip the other BASELINE.json configurations (configs object)")
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaled, skewed, rebalanced leg (N > 1)")
     ap.add_argument("--no-parity", action="store_true", help="skip the accuracy statement (parity object)")
+    ap.add_argument("--no-flow", action="store_true", help="skip the consecutive-flow-steps leg (flow_steps object, N = 1)")
+    ap.add_argument("--flow-cells", type=int, default=1 << 20, help="cells of the consecutive-flow-steps leg")
     ap.add_argument("--strong-cells", type=int, default=4194304, help="total cells of the strong-scaled leg")
     ap.add_argument("--balance-algorithm", default="allAverage", choices=["allAverage", "headTail"])
     args = ap.parse_args()
@@ -483,6 +485,11 @@ def main():
         c5 = c5_leg(args, None, lib, dev, stream, time_steps, 1, torch, local=local)
         configs["c5_drm19_real_flame_262144"] = c5["c5"]
 
+    # ---- consecutive flow steps: chemistry -> Y update -> correctThermo, deltaTChem carried or not (N = 1) ----
+    flow = None
+    if world == 1 and not args.no_flow and args.workload == "synthetic" and not args.thermo_only:
+        flow = flow_leg(args, lib, dev, stream, torch, local)
+
     if rank == 0:
         pk = ctypes.c_double()
         rc = lib.dfchem_bench_fp64_peak(local, ctypes.byref(pk))
@@ -515,6 +522,8 @@ def main():
                "integrator_stats": istats}
         if strong is not None:
             out["strong"] = strong
+        if flow is not None:
+            out["flow_steps"] = flow
         if configs is not None:
             out["configs"] = configs
         if thermo is not None:
@@ -562,6 +571,74 @@ def load_transport(h, mech, synth):
     visc, cond, diff = synth.synthetic_transport_fits(h.W)
     h.set_transport_fits(visc, cond, diff)
     return "synthetic (Cantera's ln T polynomial form)"
+
+
+def flow_leg(args, lib, dev, stream, torch, local, steps=4):
+    """What a running flow solver sees: the same cells through `steps` consecutive flow steps -- chemistry sub-step, Y += RR dt/rho,
+    correctThermo at constant enthalpy (T, psi, rho follow) -- once with every sub-step cold-started (the reference's CVODE path:
+    a new ReactorNet per cell and call, dfChemistryModel.C:748-764) and once with the deltaTChem field carried from step to step
+    (dfchem_bind_deltaTChem: the warm start of OpenFOAM's StandardChemistryModel, part of the boundary).  Reported per flow step:
+    chemistry time and step attempts per cell; and how far the two final states are apart in units of the tolerance."""
+    import dfchem_host
+    from dfchem_host import synth
+
+    h = dfchem_host.Handle(synth.load_blob(args.mech), local)
+    h.set_tolerances(args.rtol, args.atol)
+    n, N, dt = args.flow_cells, h.N, args.dt
+    b = synth.make_batch(args.mech, h.species, h.W, n, seed=12345)
+    res, finals = {}, {}
+    for mode in ("cold_start", "deltaTChem_carried"):
+        T = torch.from_numpy(b["T"]).to(dev)
+        p = torch.from_numpy(b["p"]).to(dev)
+        Y = torch.from_numpy(np.ascontiguousarray(b["Y"])).to(dev)
+        Y /= Y.sum(0, keepdim=True)
+        he, psi, rho, Q, cost = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(5))
+        RR = torch.empty((N, n), dtype=torch.float64, device=dev)
+        stat = torch.empty(n, dtype=torch.int32, device=dev)
+        dtc = torch.zeros(n, dtype=torch.float64, device=dev)
+        h.check(lib.dfchem_h_from_T_dev(h.h, n, T.data_ptr(), Y.data_ptr(), n, he.data_ptr(), stream.cuda_stream))
+
+        def thermo():
+            h.check(lib.dfchem_correct_thermo_dev(h.h, n, he.data_ptr(), p.data_ptr(), Y.data_ptr(), n, T.data_ptr(), psi.data_ptr(),
+                                                  rho.data_ptr(), None, None, n, stream.cuda_stream))
+
+        thermo()
+        h.bind_deltaTChem(dtc.data_ptr() if mode == "deltaTChem_carried" else None)
+        ms, att, amax = [], [], []
+        for _ in range(steps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record(stream)
+            h.check(lib.dfchem_solve_dev(h.h, n, T.data_ptr(), p.data_ptr(), rho.data_ptr(), None, dt, Y.data_ptr(), n, RR.data_ptr(), n,
+                                         Q.data_ptr(), cost.data_ptr(), stat.data_ptr(), stream.cuda_stream))
+            e1.record(stream)
+            torch.cuda.synchronize()
+            assert int((stat != 0).sum().item()) == 0
+            ms.append(e0.elapsed_time(e1))
+            att.append(float(cost.mean().item()))
+            amax.append(float(cost.max().item()))
+            Y += RR * (dt / rho)[None, :]
+            Y.clamp_(min=0.0)
+            Y /= Y.sum(0, keepdim=True)
+            thermo()
+        h.bind_deltaTChem(None)
+        torch.cuda.synchronize()
+        finals[mode] = (Y.clone(), T.clone())
+        res[mode] = {"ms_chemistry_per_flow_step": ms, "mean_attempts_per_cell": att, "max_attempts_per_cell": amax,
+                     "cells_per_s_last_step": n / (ms[-1] * 1e-3)}
+    Yc, Tc = finals["cold_start"]
+    Yw, Tw = finals["deltaTChem_carried"]
+    per_cell = ((Yw - Yc).abs() / (args.rtol * Yc.abs() + args.atol)).max(0).values
+    tol_units = per_cell.max().item()
+    tol_p99 = torch.quantile(per_cell[: 1 << 23], 0.99).item()
+    h.close()
+    return {"workload": f"{args.mech}, {n} synthetic cells (the headline batch's first cells), {steps} consecutive flow steps of deltaT = {dt:g} s: "
+                        "chemistry sub-step, Y += RR dt/rho, correctThermo at constant enthalpy; rtol/atol as the headline",
+            **res, "final_state_difference": {"max_abs_dY_in_tolerance_units": tol_units, "p99_abs_dY_in_tolerance_units": tol_p99,
+                                              "max_abs_dT_K": float((Tw - Tc).abs().max().item()),
+                                              "note": "carried vs cold after the last flow step, per-cell maximum over the species; tolerance unit = "
+                                                      "rtol |Y| + atol per step; cells in the induction phase of an ignition amplify any "
+                                                      "tolerance-level difference exponentially from step to step (the maximum), the bulk does not (p99)"}}
 
 
 def c5_leg(args, h, lib, dev, stream, time_steps, world, torch, local=0):
