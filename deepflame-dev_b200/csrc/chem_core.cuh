@@ -62,7 +62,7 @@ constexpr int kCellOk = 0, kCellMaxSteps = 1, kCellUnderflow = 2;  // = DFCHEM_C
 constexpr int kStages = 6;
 constexpr double kGamma = 0.25;
 constexpr int kOrder = 4;
-DFC_HD double rodas_a(int i, int j) {
+constexpr DFC_HD double rodas_a(int i, int j) {
     switch (i * 8 + j) {
         case 1 * 8 + 0: return 0.1544000000000000e+01;
         case 2 * 8 + 0: return 0.9466785280815826;
@@ -78,7 +78,7 @@ DFC_HD double rodas_a(int i, int j) {
         default: return 0.0;
     }
 }
-DFC_HD double rodas_c(int i, int j) {
+constexpr DFC_HD double rodas_c(int i, int j) {
     switch (i * 8 + j) {
         case 1 * 8 + 0: return -0.5668800000000000e+01;
         case 2 * 8 + 0: return -0.2430093356833875e+01;

@@ -184,15 +184,7 @@ DFC_HD void lpc_rate(const LpcMech& m, const double* L, int off_cx, int r, const
     const double rkc = LPC_AT(m.off_rkc, r);
     double dkdM = 0.0;
     if (kind != (uint32_t)kElementary) {
-        const double* ef = m.eff + (size_t)(x.y >> 20) * m.N;
-        double M0 = 0.0, M1 = 0.0;
-        int k = 0;
-        for (; k + 1 < m.N; k += 2) {
-            M0 = fma(ef[k], LPC_AT(off_cx, k), M0);
-            M1 = fma(ef[k + 1], LPC_AT(off_cx, k + 1), M1);
-        }
-        if (k < m.N) M0 = fma(ef[k], LPC_AT(off_cx, k), M0);
-        const double M = M0 + M1;
+        const double M = LPC_AT(m.off_M, x.y >> 20);  // third-body concentration of this reaction's efficiency set
         if (kind == (uint32_t)kThreeBody) {
             dkdM = kfe;
             kfe *= M;
@@ -258,6 +250,18 @@ DFC_HD void lpc_rate_store(const LpcMech& m, double* L, int r, const LpcRx& x, c
 template <bool JAC>
 DFC_HD void lpc_reactions(const LpcMech& m, double* L, int off_cx, double* qf_out = nullptr, double* qr_out = nullptr,
                           size_t ldq = 0) {
+    // third-body concentrations, once per efficiency set instead of once per reaction
+    for (int sset = 0; sset < m.n_msets; ++sset) {
+        const double* ef = m.eff + (size_t)sset * m.N;
+        double M0 = 0.0, M1 = 0.0;
+        int k = 0;
+        for (; k + 1 < m.N; k += 2) {
+            M0 = fma(ef[k], LPC_AT(off_cx, k), M0);
+            M1 = fma(ef[k + 1], LPC_AT(off_cx, k + 1), M1);
+        }
+        if (k < m.N) M0 = fma(ef[k], LPC_AT(off_cx, k), M0);
+        LPC_AT(m.off_M, sset) = M0 + M1;
+    }
     int r = 0;
 #if LPC_PAIR
     DFC_NOUNROLL
@@ -393,6 +397,29 @@ DFC_HD void lpc_begin_cell(const LpcMech& m, double* L, const SolveArgs& a, int 
 // the six stages are one loop body (the coefficient of a (stage, j) pair is looked up once and applied to all
 // rows; same operation order per row as the unrolled form, so the results are identical).
 #if LPC_ROLLED
+// RODAS4 coefficients for a run-time (stage, j) pair: constant memory on the device
+#define LPC_TAB_ROW(f, i) f(i, 0), f(i, 1), f(i, 2), f(i, 3), f(i, 4), f(i, 5)
+#define LPC_TAB(f) {LPC_TAB_ROW(f, 0), LPC_TAB_ROW(f, 1), LPC_TAB_ROW(f, 2), LPC_TAB_ROW(f, 3), LPC_TAB_ROW(f, 4), LPC_TAB_ROW(f, 5)}
+#if defined(__CUDACC__)
+__constant__ double lpc_tab_a[36] = LPC_TAB(rodas_a);
+__constant__ double lpc_tab_c[36] = LPC_TAB(rodas_c);
+#endif
+static const double lpc_tab_a_host[36] = LPC_TAB(rodas_a);
+static const double lpc_tab_c_host[36] = LPC_TAB(rodas_c);
+DFC_HD double lpc_a(int i, int j) {
+#ifdef __CUDA_ARCH__
+    return lpc_tab_a[i * 6 + j];
+#else
+    return lpc_tab_a_host[i * 6 + j];
+#endif
+}
+DFC_HD double lpc_c(int i, int j) {
+#ifdef __CUDA_ARCH__
+    return lpc_tab_c[i * 6 + j];
+#else
+    return lpc_tab_c_host[i * 6 + j];
+#endif
+}
 template <int NAP>
 DFC_HD void lpc_stage(const LpcMech& m, double* L, const double (&A)[NAP][NAP], double ih, int i) {
     using F = LpcFixed<NAP>;
@@ -405,7 +432,7 @@ DFC_HD void lpc_stage(const LpcMech& m, double* L, const double (&A)[NAP][NAP], 
         DFC_UNROLL
         for (int row = 0; row < NAP; ++row) v[row] = LPC_AT(m.off_c, row);
         for (int j = 0; j < i; ++j) {
-            const double aj = rodas_a(i, j);
+            const double aj = lpc_a(i, j);
             DFC_UNROLL
             for (int row = 0; row < NAP; ++row) v[row] = fma(aj, LPC_AT(F::K, j * NAP + row), v[row]);
         }
@@ -414,7 +441,7 @@ DFC_HD void lpc_stage(const LpcMech& m, double* L, const double (&A)[NAP][NAP], 
             if (row < m.NA) LPC_AT(m.off_cs, row) = v[row];
         lpc_eval<NAP, false>(m, L, m.off_cs, x);
         for (int j = 0; j < i; ++j) {
-            const double cj = rodas_c(i, j) * ih;
+            const double cj = lpc_c(i, j) * ih;
             DFC_UNROLL
             for (int row = 0; row < NAP; ++row) x[row] = fma(cj, LPC_AT(F::K, j * NAP + row), x[row]);
         }

@@ -226,6 +226,7 @@ HostLpc build_lpc_tables(const Mechanism& m, const std::vector<int>& perm, int N
     L.off_rkc = take(R);
     L.off_k0 = take(n_fall);
     L.off_lfc = take(n_fall);
+    L.off_M = take((int)sets.size());   // third-body concentration of every efficiency set, per evaluation
     L.off_q = take(std::max(R, N) + 1);   // doubles as the g/RT scratch of the set-up; last slot: 0.0 (list padding)
     L.f_rows = f_rows;
     L.q_zero = q_zero;

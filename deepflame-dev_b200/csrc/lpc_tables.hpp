@@ -41,7 +41,7 @@ struct LpcRx {
 // the padded active-species count only come first, at compile-time offsets (lane_cell.cuh: LpcFixed<NAP>).
 struct LpcMech {
     int N, NA, NAP, R, n_msets, n_fall, n_dq;
-    int off_c, off_cs, off_kf, off_rkc, off_k0, off_lfc, off_q, off_dq, lane_doubles;
+    int off_c, off_cs, off_kf, off_rkc, off_k0, off_lfc, off_M, off_q, off_dq, lane_doubles;
     // tables (one contiguous blob; staged into shared memory by every CTA)
     const uint8_t* base;
     int bytes;
