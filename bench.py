@@ -507,7 +507,7 @@ def main():
         roof = {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                 "frac": (achieved / peak) if (achieved and peak) else None, "traffic": traffic,
                 "peak_source": "dfchem_bench_fp64_peak (DFMA microbenchmark, measured in this run; MEASURED_PEAKS.json has no FP64 entry)",
-                "kernel": "solve_kernel", "algorithmic_flops_per_launch": flops,
+                "kernel": lib.dfchem_solver_name(h.h).decode(), "algorithmic_flops_per_launch": flops,
                 "flop_model": "SURVEY 8d with N = all species of the mechanism (36 for gri30; the kernel factorises the 34 active ones)",
                 "hbm_algorithmic_GBps": (2 * N + 6) * 8 * n / (ms_local * 1e-3) / 1e9,
                 "step_attempts_per_s": (cnt["accepted"] + cnt["rejected"]) / (ms_local * 1e-3)}

@@ -85,7 +85,7 @@ struct dfchem_ctx {
     void* d_lpc = nullptr;
     LpcMech lm{};
     int lpc_warps = 0;                        // > 0: dfchem_solve* run lpc_solve_kernel
-    std::string err;
+    std::string err, solver_name;
 };
 
 namespace {
@@ -311,6 +311,13 @@ int finish_create(dfchem_ctx* h, int device, dfchem_handle* out) {
 extern "C" {
 
 const char* dfchem_version(void) { return "dfchem-b200 0.1 (sm_100a)"; }
+const char* dfchem_solver_name(dfchem_handle h) {
+    if (!h) return "";
+    if (h->solver_name.empty())
+        h->solver_name = h->lpc_warps > 0 ? "lpc_solve_kernel<" + std::to_string(h->lm.NAP) + ">"
+                                          : "solve_kernel<" + std::to_string(h->dm.NP) + "," + std::to_string(h->dm.NP > 32 ? 2 : 1) + ">";
+    return h->solver_name.c_str();
+}
 
 int dfchem_create(const char* mech_yaml_path, int device, dfchem_handle* out) {
     if (!mech_yaml_path || !out) return fail(nullptr, DFCHEM_EINVAL, "null argument");

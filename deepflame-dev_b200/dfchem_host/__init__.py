@@ -79,6 +79,7 @@ SIGNATURES = {
     "dfchem_balance_stats": (c_int, [c_void_p, _dp]),
     "dfchem_bench_fp64_peak": (c_int, [c_int, _dp]),
     "dfchem_version": (c_char_p, []),
+    "dfchem_solver_name": (c_char_p, [c_void_p]),
 }
 
 _lib = None
