@@ -115,6 +115,8 @@ cudaError_t configure_t(dfchem_ctx* h) {
     // persistent CTA, one per SM: as many warps (cells in flight) as shared memory allows
     const size_t cell = (size_t)h->dm.cell_doubles * sizeof(double);
     h->warps = (int)std::min<size_t>(max_warps(NP), ((size_t)max_optin - h->dm.hot_bytes) / cell);
+    // measurement knob: fewer cells in flight per SM (how throughput scales with resident warps)
+    if (const char* cap = std::getenv("DFCHEM_MAX_WARPS")) h->warps = std::max(1, std::min(h->warps, std::atoi(cap)));
     if (h->warps < 1) return cudaErrorLaunchOutOfResources;
     // the attribute is per kernel instantiation and shared by every handle using it: always the
     // device maximum, never this handle's size
