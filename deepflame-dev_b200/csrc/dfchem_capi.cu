@@ -84,7 +84,10 @@ struct dfchem_ctx {
     HostLpc lpc;                              // lane-per-cell tables (small mechanisms)
     void* d_lpc = nullptr;
     LpcMech lm{};
-    int lpc_warps = 0;                        // > 0: dfchem_solve* run lpc_solve_kernel
+    int lpc_warps = 0;                        // > 0: dfchem_solve* run lpc_solve_kernel on batches of at least lpc_min_cells
+    int lpc_min_cells = 0;
+    bool call_lane = false;                   // the current solve call runs the lane kernel (begin_solve_call)
+    bool have_call = false;
     std::string err, solver_name;
 };
 
@@ -171,7 +174,11 @@ int take_slot(dfchem_ctx* h, cudaStream_t s, unsigned int** queue, unsigned long
     return DFCHEM_OK;
 }
 
-void begin_solve_call(dfchem_ctx* h) {
+// nC: the cells of the whole call.  The kernel is chosen once per call, so that every chunk of a host-pointer call and the
+// guest and resident launches of a balanced call run the same code (same bits for the same cell).
+void begin_solve_call(dfchem_ctx* h, int nC) {
+    h->call_lane = h->lpc_warps > 0 && nC >= h->lpc_min_cells;
+    h->have_call = true;
     h->call_first = h->seq;
     h->call_n = 0;
     h->call_acc[0] = h->call_acc[1] = h->call_acc[2] = 0;
@@ -197,7 +204,7 @@ int launch_solve(dfchem_ctx* h, const SolveArgs& a, cudaStream_t s) {
     // (the handle is single-caller, include/dfchem.h)
     int rc = take_slot(h, s, &queue, &cnt);
     if (rc != DFCHEM_OK) return rc;
-    if (h->lpc_warps > 0) {
+    if (h->call_lane) {
         const int per_cta = h->lpc_warps * kLpcLanes;
         const int grid = std::max(1, std::min(h->sm_count, (a.nC + per_cta - 1) / per_cta));
 #define CALL(NAP) lpc_solve_kernel<NAP><<<grid, per_cta, lpc_smem_bytes(h), s>>>(h->lm, a, queue, cnt)
@@ -301,6 +308,14 @@ int finish_create(dfchem_ctx* h, int device, dfchem_handle* out) {
 #undef CALL
                 if (e != cudaSuccess) return bail("cudaFuncSetAttribute(lpc_solve_kernel)", e);
                 h->lpc_warps = warps;
+                // A lane holds a cell for its whole integration: the lane kernel needs tens of thousands of cells to fill the
+                // GPU (148 SMs x warps x 32 lanes) and a batch takes at least as long as its longest cell, which is 2-3x the
+                // warp kernel's per-cell latency.  Measured (profiles/r2/small_batches_lane_vs_warp.json, ms per sub-step, lane /
+                // warp): es80 1000 cells 4.1 / 1.9, 8192 cells 4.4 / 3.3, 16384 cells 4.4 / 5.3; h2_li 6.5 / 2.7, 6.6 / 4.8,
+                // 6.7 / 8.2; c7_onestep (one reaction, 4.6 attempts) 0.12 / 0.16 at 1000 cells.  So small batches of a multi-
+                // reaction mechanism (df0DFoam's 1000 cells, config C1) go one warp per cell.  DFCHEM_LANE_MIN_CELLS overrides.
+                const char* mc = std::getenv("DFCHEM_LANE_MIN_CELLS");
+                h->lpc_min_cells = mc ? std::max(0, std::atoi(mc)) : (solver == "lane" || h->mech.R <= 4 ? 0 : 12288);
             }
         }
     }
@@ -315,9 +330,9 @@ extern "C" {
 const char* dfchem_version(void) { return "dfchem-b200 0.1 (sm_100a)"; }
 const char* dfchem_solver_name(dfchem_handle h) {
     if (!h) return "";
-    if (h->solver_name.empty())
-        h->solver_name = h->lpc_warps > 0 ? "lpc_solve_kernel<" + std::to_string(h->lm.NAP) + ">"
-                                          : "solve_kernel<" + std::to_string(h->dm.NP) + "," + std::to_string(h->dm.NP > 32 ? 2 : 1) + ">";
+    const bool lane = h->have_call ? h->call_lane : h->lpc_warps > 0;
+    h->solver_name = lane ? "lpc_solve_kernel<" + std::to_string(h->lm.NAP) + ">"
+                          : "solve_kernel<" + std::to_string(h->dm.NP) + "," + std::to_string(h->dm.NP > 32 ? 2 : 1) + ">";
     return h->solver_name.c_str();
 }
 
@@ -424,7 +439,7 @@ int dfchem_solve_dev(dfchem_handle h, int nC, const double* T, const double* p, 
         return fail(h, DFCHEM_EINVAL, "dfchem_solve_dev: bad argument");
     CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    begin_solve_call(h);
+    begin_solve_call(h, nC);
     if (nC == 0) return DFCHEM_OK;
     SolveArgs a{nC, T, p, rho, dt, dt_uniform, Y, ldY, RR, ldRR, Qdot, cost, status, h->rtol, h->atol, h->max_steps, h->dtchem};
     return launch_solve(h, a, s);
@@ -438,7 +453,7 @@ int solve_host(dfchem_ctx* h, int nC, const double* T, const double* p, const do
                double dt_uniform, const double* Y, int ldY, const double* const* Yptrs, double* RR, int ldRR,
                double* const* RRptrs, double* Qdot, double* cost, int* status) {
     CUDA_TRY(h, cudaSetDevice(h->device));
-    begin_solve_call(h);
+    begin_solve_call(h, nC);
     const int N = h->mech.N;
     const int chunk = 1 << 18;
     int rc = DFCHEM_OK;
@@ -1211,7 +1226,7 @@ int dfchem_solve_balanced_dev(dfchem_handle h, int nC, const double* T, const do
     CUDA_TRY(h, cudaSetDevice(h->device));
     NcclApi& nc = nccl_api();
     const int n = h->nranks, me = h->rank, N = h->mech.N;
-    begin_solve_call(h);
+    begin_solve_call(h, nC);
 
     // ---- plan on the device: prefix sum of the cost, all-gather of the loads, pairing + split, all-gather of counts
     CUDA_TRY(h, cudaEventRecord(h->ev[0], s));

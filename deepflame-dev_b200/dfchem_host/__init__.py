@@ -216,6 +216,10 @@ class Handle:
         self.check(self.lib.dfchem_wdot(self.h, nC, _ptr(T), _ptr(p), _ptr(Y), Y.shape[1], _ptr(out), nC))
         return out
 
+    def solver_name(self):
+        """Kernel that solve() launches on large batches (dfchem_solver_name)."""
+        return self.lib.dfchem_solver_name(self.h).decode()
+
     def wdot_static(self, T, p, Y):
         """dfchem_wdot through the allocation-free entry point (static device scratch, include/dfchem.h)."""
         nC = T.shape[0]

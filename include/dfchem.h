@@ -286,8 +286,11 @@ int dfchem_balance_stats(dfchem_handle h, double out[8]);
 int dfchem_bench_fp64_peak(int device, double* tflops);
 
 const char* dfchem_version(void);
-/* Name of the kernel that dfchem_solve* of this handle launch ("solve_kernel<34,2>": warp per cell; "lpc_solve_kernel<6>": lane per
- * cell, mechanisms with at most 8 active species or DFCHEM_SOLVER=lane).  For measurement records; no reference counterpart. */
+/* Name of the kernel that the last dfchem_solve* call of this handle launched -- before the first call: the one it launches on
+ * large batches -- ("solve_kernel<34,2>": warp per cell;
+ * "lpc_solve_kernel<6>": lane per cell, mechanisms with at most 8 active species or DFCHEM_SOLVER=lane; batches below 12288 cells
+ * of such a mechanism still run one warp per cell, which finishes a small batch sooner).  For measurement records; no reference
+ * counterpart. */
 const char* dfchem_solver_name(dfchem_handle h);
 
 #ifdef __cplusplus

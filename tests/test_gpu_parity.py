@@ -72,6 +72,36 @@ def test_solve_parity_with_golden(handles, name):
     assert c["failed"] == 0 and c["accepted"] + c["rejected"] == int(cost.sum()) and c["launches"] >= 1
 
 
+@pytest.mark.parametrize("name", ["es80", "h2_li", "c7_onestep"])
+def test_lane_per_cell_kernel_parity_with_golden(built, handles, monkeypatch, name):
+    """The lane-per-cell kernel is the library's choice for these mechanisms from 12288 cells up (every cell batch of a
+    flow solver); the 256-cell goldens would otherwise only reach the warp-per-cell kernel.  Forced here: golden parity at
+    the tight tolerance, and agreement with the warp kernel far below the tolerance at the timed one."""
+    import dfchem_host
+    from dfchem_host import synth
+
+    g = golden(name)
+    monkeypatch.setenv("DFCHEM_SOLVER", "lane")
+    hl = dfchem_host.Handle(synth.load_blob(name), 0)
+    monkeypatch.delenv("DFCHEM_SOLVER")
+    try:
+        assert hl.solver_name().startswith("lpc_solve_kernel<")
+        hw = handles(name)
+        RR, Q, cost, st = solve_golden(hl, g, 1e-11, 1e-20)
+        assert (st == 0).all()
+        err = rr_parity_error(RR, g["RR"], g["Y"], g["rho"], g["dt"])
+        assert err.max() <= 1.0, (name, float(err.max()))
+        RRl, Ql, costl, stl = solve_golden(hl, g, 1e-6, 1e-10)
+        RRw, Qw, costw, stw = solve_golden(hw, g, 1e-6, 1e-10)
+        assert (stl == 0).all() and (stw == 0).all()
+        same = costl == costw
+        assert same.mean() >= 0.95
+        floor = (g["rho"] / g["dt"])[None] * (1e-6 * np.abs(g["Y"]) + 1e-10)
+        assert (np.abs(RRl - RRw)[:, same] <= 1e-3 * floor[:, same] + 1e-9 * np.abs(RRw)[:, same]).all()
+    finally:
+        hl.close()
+
+
 def test_reference_tolerances_stay_close(handles):
     g = golden("gri30")
     RR, Q, cost, st = solve_golden(handles("gri30"), g, 1e-6, 1e-10)

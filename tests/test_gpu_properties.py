@@ -52,8 +52,10 @@ def test_conservation_and_determinism_at_scale(api, name, n):
     RR2, Q2 = h.solve(b["T"], b["p"], b["rho"], 1e-6, b["Y"])
     assert np.array_equal(RR, RR2) and np.array_equal(Q, Q2)
     # RR is linear in the caller's density (it only scales the result, dfChemistryModel.C:770)
-    RR3, _ = h.solve(b["T"][:4096], b["p"][:4096], 2.0 * b["rho"][:4096], 1e-6, np.ascontiguousarray(b["Y"][:, :4096]))
-    assert np.array_equal(RR3, 2.0 * RR[:, :4096])
+    # (16384 cells: a batch of an H2-class mechanism below 12288 cells runs the other solve kernel, whose sums differ in the last bits)
+    k = 16384
+    RR3, _ = h.solve(b["T"][:k], b["p"][:k], 2.0 * b["rho"][:k], 1e-6, np.ascontiguousarray(b["Y"][:, :k]))
+    assert np.array_equal(RR3, 2.0 * RR[:, :k])
     h.close()
 
 
