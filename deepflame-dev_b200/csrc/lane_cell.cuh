@@ -25,12 +25,6 @@ constexpr int kLS = 1;
 constexpr int kLpcLanes = 32;
 
 #define LPC_AT(off, i) L[((off) + (i)) * kLS]
-#ifndef LPC_PAIR
-#define LPC_PAIR 0   // reaction loop by pairs: measured +2 % on es80, -18 % on h2_li, -6 % on c7_onestep (profiles/r2): off
-#endif
-#ifndef LPC_ROLLED
-#define LPC_ROLLED 1  // the six RODAS stages as a real loop (a third less code)
-#endif
 
 struct LpcState {  // per-lane integrator state (registers)
     double t, h, dt, rho_ct, ysum, h_free;
@@ -142,8 +136,7 @@ DFC_HD void lpc_setup(const LpcMech& m, double* L, double T) {
 
 // Rate of progress of reaction r at the concentrations in column off_cx, all in registers: q, the forward and
 // reverse parts, and (if JAC) the partial derivatives in slot order (present reactant factors, present product
-// factors, d q/d[M]); `mask` bit a = derivative a is present.  Loads only: two calls in a row have no store
-// between their loads, so the compiler can overlap the load -> multiply chains of two reactions.
+// factors, d q/d[M]); `mask` bit a = derivative a is present.  Loads and arithmetic only; lpc_rate_store writes.
 struct LpcRate {
     double q, qf, qr, d[7];
     uint32_t mask;
@@ -245,8 +238,7 @@ DFC_HD void lpc_rate_store(const LpcMech& m, double* L, int r, const LpcRx& x, c
     }
 }
 
-// Reaction loop: q_r -> column off_q (and, if JAC, the partial derivatives -> column off_dq), two reactions per
-// iteration (all loads of both before the first store).
+// Reaction loop: q_r -> column off_q (and, if JAC, the partial derivatives -> column off_dq).
 template <bool JAC>
 DFC_HD void lpc_reactions(const LpcMech& m, double* L, int off_cx, double* qf_out = nullptr, double* qr_out = nullptr,
                           size_t ldq = 0) {
@@ -263,17 +255,6 @@ DFC_HD void lpc_reactions(const LpcMech& m, double* L, int off_cx, double* qf_ou
         LPC_AT(m.off_M, sset) = M0 + M1;
     }
     int r = 0;
-#if LPC_PAIR
-    DFC_NOUNROLL
-    for (; r + 1 < m.R; r += 2) {
-        const LpcRx x0 = m.rx[r], x1 = m.rx[r + 1];
-        LpcRate o0, o1;
-        lpc_rate<JAC>(m, L, off_cx, r, x0, o0);
-        lpc_rate<JAC>(m, L, off_cx, r + 1, x1, o1);
-        lpc_rate_store<JAC>(m, L, r, x0, o0, qf_out, qr_out, ldq);
-        lpc_rate_store<JAC>(m, L, r + 1, x1, o1, qf_out, qr_out, ldq);
-    }
-#endif
     DFC_NOUNROLL
     for (; r < m.R; ++r) {
         const LpcRx x = m.rx[r];
@@ -393,10 +374,9 @@ DFC_HD void lpc_begin_cell(const LpcMech& m, double* L, const SolveArgs& a, int 
     }
 }
 
-// stage i of RODAS4: stage point, rate evaluation, right-hand side, solve.  LPC_ROLLED: i is a run-time value and
+// stage i of RODAS4: stage point, rate evaluation, right-hand side, solve.  i is a run-time value and
 // the six stages are one loop body (the coefficient of a (stage, j) pair is looked up once and applied to all
 // rows; same operation order per row as the unrolled form, so the results are identical).
-#if LPC_ROLLED
 // RODAS4 coefficients for a run-time (stage, j) pair: constant memory on the device
 #define LPC_TAB_ROW(f, i) f(i, 0), f(i, 1), f(i, 2), f(i, 3), f(i, 4), f(i, 5)
 #define LPC_TAB(f) {LPC_TAB_ROW(f, 0), LPC_TAB_ROW(f, 1), LPC_TAB_ROW(f, 2), LPC_TAB_ROW(f, 3), LPC_TAB_ROW(f, 4), LPC_TAB_ROW(f, 5)}
@@ -450,35 +430,6 @@ DFC_HD void lpc_stage(const LpcMech& m, double* L, const double (&A)[NAP][NAP], 
     DFC_UNROLL
     for (int row = 0; row < NAP; ++row) LPC_AT(F::K, i * NAP + row) = x[row];
 }
-#else
-template <int NAP, int I>
-DFC_HD void lpc_stage(const LpcMech& m, double* L, const double (&A)[NAP][NAP], double ih) {
-    using F = LpcFixed<NAP>;
-    double x[NAP];
-    if (I == 0) {
-        DFC_UNROLL
-        for (int row = 0; row < NAP; ++row) x[row] = LPC_AT(F::F0, row);
-    } else {
-        DFC_UNROLL
-        for (int row = 0; row < NAP; ++row) {
-            double v = LPC_AT(m.off_c, row);
-            DFC_UNROLL
-            for (int j = 0; j < I; ++j)
-                if (rodas_a(I, j) != 0.0) v = fma(rodas_a(I, j), LPC_AT(F::K, j * NAP + row), v);
-            if (row < m.NA) LPC_AT(m.off_cs, row) = v;
-        }
-        lpc_eval<NAP, false>(m, L, m.off_cs, x);
-        DFC_UNROLL
-        for (int row = 0; row < NAP; ++row) {
-            DFC_UNROLL
-            for (int j = 0; j < I; ++j) x[row] = fma(rodas_c(I, j) * ih, LPC_AT(F::K, j * NAP + row), x[row]);
-        }
-    }
-    lpc_lu_solve<NAP>(L, A, x);
-    DFC_UNROLL
-    for (int row = 0; row < NAP; ++row) LPC_AT(F::K, I * NAP + row) = x[row];
-}
-#endif
 
 // One step attempt of the cell on this lane (the body of integrate_cell's loops).  Returns true
 // when the sub-step is complete (or has failed: S.status).
@@ -525,17 +476,8 @@ DFC_HD bool lpc_attempt(const LpcMech& m, double* L, LpcState& S, double rtol, d
         S.h = hs * kFacUnstable;
         return false;
     }
-#if LPC_ROLLED
     DFC_NOUNROLL
     for (int i = 0; i < kStages; ++i) lpc_stage<NAP>(m, L, A, ih, i);
-#else
-    lpc_stage<NAP, 0>(m, L, A, ih);
-    lpc_stage<NAP, 1>(m, L, A, ih);
-    lpc_stage<NAP, 2>(m, L, A, ih);
-    lpc_stage<NAP, 3>(m, L, A, ih);
-    lpc_stage<NAP, 4>(m, L, A, ih);
-    lpc_stage<NAP, 5>(m, L, A, ih);
-#endif
     // new solution = argument of the last stage + k_6; error estimate = k_6
     double inc[NAP];
     double e2 = 0.0;
