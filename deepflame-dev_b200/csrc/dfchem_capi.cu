@@ -207,7 +207,7 @@ int launch_solve(dfchem_ctx* h, const SolveArgs& a, cudaStream_t s) {
     if (h->call_lane) {
         const int per_cta = h->lpc_warps * kLpcLanes;
         const int grid = std::max(1, std::min(h->sm_count, (a.nC + per_cta - 1) / per_cta));
-#define CALL(NAP) lpc_solve_kernel<NAP><<<grid, per_cta, lpc_smem_bytes(h), s>>>(h->lm, a, queue, cnt)
+#define CALL(NAP) lpc_solve_kernel<NAP><<<grid, per_cta, lpc_smem_bytes(h), s>>>(h->lm, a, queue, cnt, h->mech.R <= 4 ? 16 : 4)
         DFC_DISPATCH_LPC(h->lm.NAP, CALL)
 #undef CALL
     } else {

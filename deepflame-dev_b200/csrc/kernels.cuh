@@ -66,13 +66,15 @@ solve_kernel(const DevMech mg, const SolveArgs a, unsigned int* queue, unsigned 
 // ---- lane-per-cell solve kernel (small mechanisms: NA <= kLpcMaxActive) -------------------------
 // Persistent CTA per SM; every LANE owns one cell from load to RR/Qdot (lane_cell.cuh).  A warp runs one
 // step attempt per loop iteration for its 32 cells; lanes whose cell has finished go idle and are refilled
-// from the global queue in groups (kLpcRefill idle lanes at a time, one warp-aggregated atomic), so the
+// from the global queue in groups (`refill` idle lanes at a time, one warp-aggregated atomic), so the
 // per-cell set-up (Arrhenius / equilibrium exponentials) is paid by many lanes at once and stiff cells
-// never hold back more than their own lane.
-constexpr int kLpcRefill = 8;
+// never hold back more than their own lane.  The warp executes the set-up once per fetch whatever the number of
+// lanes in it, and an idle lane waits for the fetch: mechanisms that need tens of attempts per cell want small
+// groups (es80 / h2_li: 4 is 1-4 % faster than 8, 16 is 15-20 % slower), a one-step mechanism with 4.6 attempts per
+// cell wants large ones (c7_onestep: 16 is 27 % faster than 8); profiles/r2/lane_refill_granularity.json.
 template <int NAP>
 __global__ void __launch_bounds__(NAP <= 8 ? 256 : 128, 1)
-lpc_solve_kernel(const LpcMech mg, const SolveArgs a, unsigned int* queue, unsigned long long* counters) {
+lpc_solve_kernel(const LpcMech mg, const SolveArgs a, unsigned int* queue, unsigned long long* counters, int refill) {
     extern __shared__ double2 dfc_smem[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(dfc_smem);
     {
@@ -91,7 +93,7 @@ lpc_solve_kernel(const LpcMech mg, const SolveArgs a, unsigned int* queue, unsig
     while (true) {
         const unsigned idle = __ballot_sync(0xffffffffu, S.cell < 0);
         const int nidle = __popc(idle);
-        if (!exhausted && nidle >= kLpcRefill) {
+        if (!exhausted && nidle >= refill) {
             unsigned base = 0;
             if (lane == 0) base = atomicAdd(queue, (unsigned)nidle);
             base = __shfl_sync(0xffffffffu, base, 0);
