@@ -80,3 +80,20 @@ def test_balance_plan_matches_reference_rule(built, loads):
     assert np.all(np.diag(send) == 0) and np.all(send >= 0)
     assert np.abs(after - mean).max() <= max(0.02 * mean * len(loads), 1e-12)   # residual = dropped ops only
     assert after.max() <= max(loads) + 1e-12
+
+
+def test_static_scratch_limit_in_header_matches_the_gpu_test(built):
+    """DFCHEM_STATIC_SCRATCH_BYTES (include/dfchem.h) is the limit tests/test_zz_no_alloc.py probes; the
+    allocation-free entry point rejects bad arguments without a device (no handle -> DFCHEM_EINVAL)."""
+    import importlib
+
+    text = open(os.path.join(ROOT, "include", "dfchem.h")).read()
+    m = re.search(r"#define\s+DFCHEM_STATIC_SCRATCH_BYTES\s+\((\d+)u\s*<<\s*(\d+)\)", text)
+    assert m, "DFCHEM_STATIC_SCRATCH_BYTES not found in the header"
+    limit = int(m.group(1)) << int(m.group(2))
+    zz = importlib.import_module("test_zz_no_alloc")
+    assert zz.STATIC_BYTES == limit == 8 << 20
+    lib = dfchem_host.load_library()
+    a = np.zeros(4)
+    p = a.ctypes.data_as(ctypes.c_void_p)
+    assert lib.dfchem_wdot_static(None, 4, p, p, p, 4, p, 4) == -1
