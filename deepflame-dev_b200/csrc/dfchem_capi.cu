@@ -281,10 +281,10 @@ int finish_create(dfchem_ctx* h, int device, dfchem_handle* out) {
     DFC_DISPATCH_NP(h->dm.NP, CALL)
 #undef CALL
     if (e != cudaSuccess) return bail("kernel configuration", e);
-    // Lane-per-cell solve kernel (lane_cell.cuh, gather form with ELL lists).  Measured on B200 (profiles/r2/lane_variants.json,
-    // 1,048,576 cells, rtol 1e-6 / atol 1e-10) against the warp-per-cell kernel: c7_onestep 2.69e8 vs 1.65e7 cells/s (16x), es80
-    // 1.2e7 vs 4.0e6 (3x), h2_li 5.5e6 vs 2.5e6 (2.2x).  Default: mechanisms with at most 8 active species (padded sizes 4 / 6 / 8;
-    // the 12-wide instantiation spills and stays opt-in); DFCHEM_SOLVER=lane / warp forces either kernel.
+    // Lane-per-cell solve kernel (lane_cell.cuh, gather form with ELL lists).  Measured on B200 (profiles/r2/lane_final.json,
+    // lane_refill_granularity.json; 1,048,576 cells, rtol 1e-6 / atol 1e-10) against the warp-per-cell kernel: c7_onestep 3.2e8 vs
+    // 1.65e7 cells/s (20x), es80 1.70e7 vs 4.0e6 (4.2x), h2_li 6.4e6 vs 2.5e6 (2.6x).  Default: mechanisms with at most 8 active
+    // species (padded sizes 4 / 6 / 8; the 12-wide instantiation spills and stays opt-in); DFCHEM_SOLVER=lane / warp forces either kernel.
     const char* solver_env = std::getenv("DFCHEM_SOLVER");
     const std::string solver = solver_env ? solver_env : "";
     constexpr int kLpcAutoActive = 8;
